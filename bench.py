@@ -1,0 +1,447 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: fused V-trace + IMPALA loss, forward+backward.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N \
+        --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+Metric (BASELINE.json): timesteps/s (T x B per call) of the fused pass and the
+HBM bandwidth it achieves.  Workload: the configuration the metric's target is
+quoted on, T=100, B=32768, A=18 per GPU (weak scaling: every rank holds its
+own B columns, only the loss scalars cross NVLink).  A "step" is one call of
+`vtr_from_logits_fused_f32` (K1 column kernel + K3 loss reduction) with every
+output materialised, plus, for N>1, the all-gather of the loss scalars.
+
+Prints ONE JSON line on rank 0.  See DESIGN.md section "Measurement".
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+  sys.path.insert(0, ROOT)
+
+T_DEFAULT, B_DEFAULT, A_DEFAULT = 100, 32768, 18
+BASELINE_COST, ENTROPY_COST = 0.5, 0.00025   # experiment.py:70-71
+METRIC = 'vtrace_impala_loss_fwd_bwd_timesteps_per_sec'
+UNIT = 'timesteps/s'
+FUSED_KEYS = ('behaviour_policy_logits', 'target_policy_logits', 'actions',
+              'discounts', 'rewards', 'values', 'bootstrap_value')
+
+
+def algorithmic_bytes(T, B, A):
+  """(12A + 40) bytes per timestep + 4B for the bootstrap."""
+  return T * B * (12 * A + 40) + 4 * B
+
+
+def measured_peak_gbs():
+  path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+  try:
+    with open(path) as f:
+      return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+  except Exception:  # pylint: disable=broad-except
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def synthetic_on_device(T, B, A, seed, device):
+  """SURVEY.md 8(d) recipe, generated on the device."""
+  import torch
+  g = torch.Generator(device=device).manual_seed(seed)
+  rn = lambda *s: torch.randn(*s, generator=g, device=device)
+  behaviour = rn(T, B, A)
+  target = behaviour + 0.5 * rn(T, B, A)
+  actions = torch.randint(0, A, (T, B), generator=g, device=device,
+                          dtype=torch.int32)
+  done = torch.rand(T, B, generator=g, device=device) < 0.01
+  rewards = (2.0 * rn(T, B)).clamp_(-1.0, 1.0)      # abs_one, experiment.py:378
+  discounts = (~done).float() * 0.99                # experiment.py:384
+  values, bootstrap = rn(T, B), rn(B)
+  return dict(behaviour_policy_logits=behaviour, target_policy_logits=target,
+              actions=actions, discounts=discounts, rewards=rewards,
+              values=values, bootstrap_value=bootstrap)
+
+
+class ClockSampler(threading.Thread):
+  """Samples SM clock and throttle reasons of one GPU through NVML."""
+
+  REASONS = {
+      0x8: 'hw_slowdown', 0x40: 'hw_thermal_slowdown',
+      0x20: 'sw_thermal_slowdown', 0x4: 'sw_power_cap',
+      0x80: 'hw_power_brake_slowdown', 0x2: 'applications_clocks_setting',
+      0x100: 'display_clock_setting', 0x10: 'sync_boost',
+  }
+
+  def __init__(self, index, period=0.002):
+    super().__init__(daemon=True)
+    self.period, self.samples, self.reason_bits = period, [], 0
+    self._stop_event = threading.Event()
+    self.sm_max = None
+    self.ok = False
+    try:
+      import pynvml
+      pynvml.nvmlInit()
+      self.nv = pynvml
+      self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+      self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+      self.ok = True
+    except Exception:  # pylint: disable=broad-except
+      self.ok = False
+
+  def run(self):
+    if not self.ok:
+      return
+    while not self._stop_event.is_set():
+      try:
+        self.samples.append(
+            self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+        self.reason_bits |= int(
+            self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+      except Exception:  # pylint: disable=broad-except
+        pass
+      time.sleep(self.period)
+
+  def stop(self):
+    self._stop_event.set()
+    if self.is_alive():
+      self.join()
+
+  def summary(self):
+    reasons = [name for bit, name in self.REASONS.items()
+               if self.reason_bits & bit]
+    return {
+        'sm_mhz': statistics.median(self.samples) if self.samples else None,
+        'sm_max_mhz': self.sm_max, 'reasons': reasons,
+        'samples': len(self.samples)}
+
+
+def physical_gpu_index(local_index):
+  vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+  if vis:
+    try:
+      return int(vis.split(',')[local_index])
+    except (ValueError, IndexError):
+      pass
+  return local_index
+
+
+# ---------------------------------------------------------------------------
+# CPU legs (the oracle's float32 op-for-op port; see oracle/cpu_port.py)
+# ---------------------------------------------------------------------------
+def time_cpu_port(T, B, A, steps, warmup, seed=1):
+  import torch
+  from oracle import cpu_port
+  from oracle import vtrace_oracle as oracle
+  cores = len(os.sched_getaffinity(0))
+  torch.set_num_threads(cores)
+  inp = oracle.synthetic_inputs(T, B, A, seed=seed)
+  args = [torch.from_numpy(inp[k]) for k in FUSED_KEYS]
+  for _ in range(warmup):
+    cpu_port.learner_loss(*args, baseline_cost=BASELINE_COST,
+                          entropy_cost=ENTROPY_COST)
+  t0 = time.perf_counter()
+  for _ in range(steps):
+    cpu_port.learner_loss(*args, baseline_cost=BASELINE_COST,
+                          entropy_cost=ENTROPY_COST)
+  dt = time.perf_counter() - t0
+  return T * B * steps / dt, dt / steps, cores
+
+
+def cpu_model():
+  try:
+    with open('/proc/cpuinfo') as f:
+      for line in f:
+        if line.startswith('model name'):
+          return line.split(':', 1)[1].strip()
+  except OSError:
+    pass
+  return 'unknown'
+
+
+def pick_cpu_sample(T, A, steps, warmup, budget_s):
+  """Largest B (<= B_DEFAULT) whose steps+warmup fit in budget_s."""
+  rate, _, _ = time_cpu_port(T, 2048, A, 3, 2)
+  for B in (32768, 16384, 8192, 4096, 2048, 1024, 512, 256):
+    if T * B * (steps + warmup) / rate <= budget_s:
+      return B
+  return 128
+
+
+def run_reference(args):
+  """--impl reference: the reference's CPU path (TF1 is not installable, so
+  the op-for-op torch-CPU port of oracle/cpu_port.py) on the host cores."""
+  rank = int(os.environ.get('RANK', '0'))
+  if rank != 0:
+    return
+  T, A = args.T, args.A
+  B = pick_cpu_sample(T, A, args.steps, args.warmup, budget_s=90.0)
+  rate, sec_per_step, cores = time_cpu_port(T, B, A, args.steps, args.warmup)
+  sample = ('T=%d B=%d A=%d per step (workload is B=%d per GPU), float32, '
+            'torch-CPU port of vtrace.py + experiment.py:324-343 with autograd '
+            'backward, %d threads, %s' % (T, B, A, args.B, cores, cpu_model()))
+  line = {
+      'impl': 'reference', 'metric': METRIC, 'value': rate, 'unit': UNIT,
+      'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+      'ms_per_step': sec_per_step * 1e3, 'higher_is_better': True,
+      'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+      'data': 'synthetic',
+      'config': {'workload': 'fused V-trace + IMPALA loss fwd+bwd, T=%d B=%d '
+                             'A=%d per GPU' % (T, args.B, A),
+                 'T': T, 'B_per_gpu': args.B, 'A': A, 'cpu_sample_B': B},
+      'cpu_baseline': {'value': rate, 'unit': UNIT, 'cores': cores,
+                       'kind': 'port', 'sample': sample},
+      'e2e': {'value': rate, 'unit': UNIT, 'h2d_bytes_per_step': 0,
+              'd2h_bytes_per_step': 0},
+      'gpu_launches': 0,
+  }
+  print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+class FusedCall(object):
+  """Pre-allocated outputs + one ctypes call into the C ABI per step."""
+
+  def __init__(self, inp, T, B, A, device):
+    import torch
+    from scalable_agent_b200 import _lib
+    self.lib = _lib.load()
+    self._lib_mod = _lib
+    f32 = dict(dtype=torch.float32, device=device)
+    self.out = {
+        'vs': torch.empty(T, B, **f32), 'pg_advantages': torch.empty(T, B, **f32),
+        'log_rhos': torch.empty(T, B, **f32),
+        'behaviour_action_log_probs': torch.empty(T, B, **f32),
+        'target_action_log_probs': torch.empty(T, B, **f32),
+        'd_target_logits': torch.empty(T, B, A, **f32),
+        'd_values': torch.empty(T, B, **f32),
+        'losses': torch.empty(4, **f32)}
+    self.ws_bytes = self.lib.vtr_fused_workspace_bytes(T, B, A)
+    self.ws = torch.empty(self.ws_bytes // 8, dtype=torch.float64, device=device)
+    p = _lib.FusedParams()
+    p.T, p.B, p.A = T, B, A
+    for k in FUSED_KEYS:
+      setattr(p, k, inp[k].data_ptr())
+    p.clip_rho_threshold = p.clip_pg_rho_threshold = 1.0   # vtrace.py:74
+    p.baseline_cost, p.entropy_cost = BASELINE_COST, ENTROPY_COST
+    for k, v in self.out.items():
+      setattr(p, k, v.data_ptr())
+    self.p = p
+    self.inp = inp
+    self.stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    self.launches_per_call = 2   # K1 fused_column_kernel + K3 reduce_losses_kernel
+
+  def __call__(self):
+    rc = self.lib.vtr_from_logits_fused_f32(
+        ctypes.byref(self.p), self.ws.data_ptr(), self.ws_bytes, self.stream)
+    if rc != 0:
+      self._lib_mod.check(rc, 'vtr_from_logits_fused_f32')
+
+
+def run_gpu(args):
+  import torch
+  import torch.distributed as dist
+
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+  if not torch.cuda.is_available():
+    raise SystemExit('bench.py: no CUDA device; the product path has no CPU '
+                     'fallback (use --impl reference for the CPU baseline)')
+  torch.cuda.set_device(local_rank)
+  device = torch.device('cuda', local_rank)
+  if world > 1:
+    dist.init_process_group('nccl', device_id=device)
+  T, B, A = args.T, args.B, args.A
+  K, W = args.steps, max(args.warmup, 3)
+
+  inp = synthetic_on_device(T, B, A, 1000 * rank + 1, device)
+  call = FusedCall(inp, T, B, A, device)
+  gathered = torch.empty(world, 4, dtype=torch.float32, device=device)
+
+  def step():
+    call()
+    if world > 1:
+      # The only cross-GPU traffic of the path: the loss scalars.  All-gather
+      # then sum in rank order keeps the total bitwise reproducible.
+      dist.all_gather_into_tensor(gathered, call.out['losses'])
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  for _ in range(W):
+    step()
+  barrier()
+
+  sampler = ClockSampler(physical_gpu_index(local_rank))
+  sampler.start()
+  starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+  ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+  t_begin = torch.cuda.Event(enable_timing=True)
+  t_end = torch.cuda.Event(enable_timing=True)
+  barrier()
+  t_begin.record()
+  for i in range(K):
+    starts[i].record()
+    call()
+    ends[i].record()
+    if world > 1:
+      dist.all_gather_into_tensor(gathered, call.out['losses'])
+  t_end.record()
+  barrier()
+  total_ms = t_begin.elapsed_time(t_end)
+  kernel_ms = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+  # keep the GPU busy a little longer if the region was too short to sample
+  if sampler.ok and len(sampler.samples) < 5:
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < 0.3:
+      for _ in range(20):
+        call()
+      torch.cuda.synchronize()
+    clock_note = 'timed region + 0.3 s probe of the same kernel'
+  else:
+    clock_note = 'timed region'
+  sampler.stop()
+
+  if world > 1:
+    t = torch.tensor([total_ms], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    km = torch.tensor([statistics.mean(kernel_ms)], dtype=torch.float64,
+                      device=device)
+    dist.all_reduce(km, op=dist.ReduceOp.MAX)
+    kernel_mean_ms = float(km.item())
+  else:
+    kernel_mean_ms = statistics.mean(kernel_ms)
+  value = T * B * world * K / (total_ms * 1e-3)
+
+  # ---- end to end through the public API with host buffers ---------------
+  from scalable_agent_b200 import experiment
+  e2e_steps = max(1, min(K, 10))
+  host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v)
+          for k, v in inp.items()}
+  h2d = sum(v.numel() * v.element_size() for v in host.values())
+
+  def e2e_step():
+    dev_in = {k: v.to(device, non_blocking=True) for k, v in host.items()}
+    dev_in['target_policy_logits'].requires_grad_(True)
+    dev_in['values'].requires_grad_(True)
+    out = experiment.compute_vtrace_loss(
+        baseline_cost=BASELINE_COST, entropy_cost=ENTROPY_COST, **dev_in)
+    out.total_loss.backward()
+    result = torch.stack([out.total_loss.detach(), out.policy_gradient_loss,
+                          out.baseline_loss, out.entropy_loss])
+    if world > 1:
+      dist.all_gather_into_tensor(gathered, result)
+      result = gathered.sum(0)
+    return result.cpu()      # device -> host read of the step's result
+
+  for _ in range(2):
+    e2e_step()
+  barrier()
+  t0 = time.perf_counter()
+  for _ in range(e2e_steps):
+    losses_host = e2e_step()
+  barrier()
+  e2e_s = time.perf_counter() - t0
+  if world > 1:
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+  e2e_value = T * B * world * e2e_steps / e2e_s
+  d2h = losses_host.numel() * losses_host.element_size()
+
+  line = None
+  if rank == 0:
+    peak, peak_src = measured_peak_gbs()
+    alg = algorithmic_bytes(T, B, A)
+    achieved = alg / (kernel_mean_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+      with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as f:
+        rec = json.load(f)
+      if rec.get('T') == T and rec.get('B') == B and rec.get('A') == A:
+        traffic = rec.get('dram_bytes_per_launch')
+    except Exception:  # pylint: disable=broad-except
+      pass
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
+        'steps': K, 'warmup': W, 'ms_per_step': total_ms / K,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'f32', 'data': 'synthetic',
+        'config': {
+            'workload': 'fused V-trace + IMPALA loss fwd+bwd, T=%d B=%d A=%d '
+                        'per GPU, all 5 V-trace fields + d_target_logits + '
+                        'd_values + 4 loss scalars written' % (T, B, A),
+            'T': T, 'B_per_gpu': B, 'A': A, 'global_B': B * world,
+            'parallelism': 'B sharded over %d rank(s); all-gather of 4 loss '
+                           'scalars per step' % world,
+            'l2': 'no flush: %.0f MB of inputs + %.0f MB of outputs per step '
+                  'exceed the 126 MB L2' % (
+                      (T * B * (8 * A + 16) + 4 * B) / 1e6,
+                      T * B * (4 * A + 24) / 1e6),
+            'clip_rho': 1.0, 'clip_pg_rho': 1.0,
+            'baseline_cost': BASELINE_COST, 'entropy_cost': ENTROPY_COST},
+        'roofline': {
+            'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+            'frac': achieved / peak, 'traffic': traffic,
+            'peak_source': peak_src,
+            'algorithmic_bytes_per_launch': alg,
+            'kernel': 'fused_column_kernel<18,true> (+ reduce_losses_kernel, '
+                      'inside the same event pair)',
+            'kernel_ms_mean': kernel_mean_ms,
+            'kernel_ms_min': min(kernel_ms),
+            'frac_of_nominal_8TBs': achieved / 8000.0},
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+                'd2h_bytes_per_step': d2h, 'steps': e2e_steps,
+                'ms_per_step': e2e_s / e2e_steps * 1e3,
+                'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + '
+                       'backward, pinned host inputs'},
+        'gpu_launches': call.launches_per_call * K,
+        'clocks': dict(sampler.summary(), sampled=clock_note),
+    }
+  if world > 1:
+    dist.barrier()
+  if rank == 0:
+    if world == 1 and not args.no_cpu_baseline:
+      Bc = pick_cpu_sample(T, A, 6, 1, budget_s=20.0)
+      rate, _, cores = time_cpu_port(T, Bc, A, 6, 1)
+      line['cpu_baseline'] = {
+          'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+          'sample': '6 steps of T=%d B=%d A=%d, float32 torch-CPU port of the '
+                    'reference path with autograd backward (oracle/cpu_port.py)'
+                    ', %s' % (T, Bc, A, cpu_model())}
+    else:
+      line['cpu_baseline'] = None
+    print(json.dumps(line), flush=True)
+  if world > 1:
+    dist.destroy_process_group()
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--steps', type=int, default=200)
+  ap.add_argument('--warmup', type=int, default=20)
+  ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+  ap.add_argument('--T', type=int, default=T_DEFAULT)
+  ap.add_argument('--B', type=int, default=B_DEFAULT, help='columns per GPU')
+  ap.add_argument('--A', type=int, default=A_DEFAULT)
+  ap.add_argument('--no-cpu-baseline', action='store_true')
+  args = ap.parse_args()
+  if args.impl == 'reference':
+    run_reference(args)
+  else:
+    run_gpu(args)
+
+
+if __name__ == '__main__':
+  main()

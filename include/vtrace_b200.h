@@ -1,0 +1,213 @@
+/*
+ * vtrace_b200.h -- C ABI of libvtrace_b200.so
+ *
+ * B200 (sm_100a) implementation of IMPALA's learner-side off-policy
+ * correction: V-trace plus the three IMPALA loss terms, forward and backward.
+ * Citations are to the reference tree (Zhehui-Huang/scalable_agent).
+ *
+ * The reference has no FFI boundary for this path: it is Python that adds
+ * TensorFlow graph nodes (vtrace.py, experiment.py:324-343) and the authors
+ * name "a custom TensorFlow operation" as the intended upgrade
+ * (experiment.py:387-388).  This header is that custom-op boundary.  Each
+ * entry point below cites the reference function it replaces.
+ *
+ * Conventions
+ *   - All tensors are C-contiguous, time-major: logits [T,B,A] (A fastest),
+ *     per-step tensors [T,B], bootstrap [B].  float = IEEE fp32, actions int32.
+ *   - Every pointer is a DEVICE pointer on the current device unless the
+ *     parameter comment says "host".  The caller owns every buffer, including
+ *     workspaces; the library never allocates, frees or keeps a pointer.
+ *   - Work is enqueued on `stream` (a cudaStream_t passed as void*); no entry
+ *     point synchronises the host.
+ *   - Return value: 0 = VTR_OK; negative = argument error detected before any
+ *     launch (VTR_ERR_*); positive = the cudaError_t of a failed launch.
+ *     vtr_last_error() returns a thread-local message for the last failure.
+ *     Nothing aborts, exits or throws.
+ *   - Pointers documented "may be NULL" switch the corresponding output off.
+ *   - Out-of-range actions are clamped to [0, A-1] for memory safety; the
+ *     results for such steps are unspecified (TF raises on CPU, vtrace.py:67).
+ */
+#ifndef VTRACE_B200_H_
+#define VTRACE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VTR_VERSION 100 /* major*10000 + minor*100 + patch */
+
+#define VTR_OK 0
+#define VTR_ERR_INVALID_ARGUMENT (-1) /* NULL required pointer, T/B/A <= 0 ... */
+#define VTR_ERR_UNSUPPORTED (-2)      /* A above VTR_MAX_ACTIONS, bad mode    */
+#define VTR_ERR_WORKSPACE (-3)        /* workspace missing or too small       */
+#define VTR_ERR_MISALIGNED (-4)       /* pointer not aligned to its element   */
+
+#define VTR_MAX_ACTIONS 256
+
+/* flags for vtr_fused_params.flags / vtr_from_importance_weights_f32 */
+#define VTR_FLAG_NO_CLIP_RHO 1u    /* clip_rho_threshold=None    (vtrace.py:236-239) */
+#define VTR_FLAG_NO_CLIP_PG_RHO 2u /* clip_pg_rho_threshold=None (vtrace.py:270-274) */
+
+/* reward clipping fused into the prologue (experiment.py:377-382) */
+#define VTR_REWARD_CLIP_NONE 0
+#define VTR_REWARD_CLIP_ABS_ONE 1         /* clip(r, -1, 1)            :378     */
+#define VTR_REWARD_CLIP_SOFT_ASYMMETRIC 2 /* tanh(r/5)*5, x0.3 if r<0  :380-382 */
+
+/* kernel selection for the fused entry point (0 = library decides) */
+#define VTR_PATH_AUTO 0
+#define VTR_PATH_COLUMN 1 /* thread-per-column, wide B                       */
+#define VTR_PATH_SCAN 2   /* T-parallel affine scan, small B                 */
+
+int vtr_version(void);
+
+/* Thread-local, never NULL; valid until the next failing call on this thread. */
+const char* vtr_last_error(void);
+
+/*
+ * Arguments of the fused forward+backward pass.
+ *
+ * Replaces, in one launch (plus one tiny reduction launch):
+ *   vtrace.from_logits                        vtrace.py:71-161
+ *     log_probs_from_logits_and_actions x2    vtrace.py:45-68, 143-146
+ *     from_importance_weights                 vtrace.py:164-280
+ *   compute_policy_gradient_loss              experiment.py:338-343
+ *   compute_baseline_loss(vs - values)        experiment.py:324-328, 404-405
+ *   compute_entropy_loss                      experiment.py:331-335
+ *   total = pg + baseline_cost*bl + entropy_cost*ent   experiment.py:401-407
+ *   the TF autodiff backward of that total    experiment.py:415
+ *   optionally the reward clip / discount glue         experiment.py:377-384
+ */
+typedef struct vtr_fused_params {
+  int32_t T; /* unroll length          (experiment.py:65)  */
+  int32_t B; /* batch                  (experiment.py:64)  */
+  int32_t A; /* number of actions, 1..VTR_MAX_ACTIONS       */
+  uint32_t flags; /* VTR_FLAG_*                              */
+
+  /* inputs */
+  const float* behaviour_policy_logits; /* [T,B,A]                        */
+  const float* target_policy_logits;    /* [T,B,A]                        */
+  const int32_t* actions;               /* [T,B]                          */
+  const float* discounts;               /* [T,B]; may be NULL iff done set */
+  const float* rewards;                 /* [T,B]                          */
+  const float* values;                  /* [T,B]                          */
+  const float* bootstrap_value;         /* [B]                            */
+  const uint8_t* done; /* [T,B] bool, may be NULL.  If set, discounts =
+                          (!done)*discounting (experiment.py:384) and the
+                          `discounts` pointer is ignored.                 */
+
+  float clip_rho_threshold;    /* ignored with VTR_FLAG_NO_CLIP_RHO       */
+  float clip_pg_rho_threshold; /* ignored with VTR_FLAG_NO_CLIP_PG_RHO    */
+  float baseline_cost;         /* experiment.py:71                        */
+  float entropy_cost;          /* experiment.py:70                        */
+  float discounting;           /* experiment.py:72, used only with `done` */
+  int32_t reward_clip_mode;    /* VTR_REWARD_CLIP_*                       */
+  int32_t path;                /* VTR_PATH_*                              */
+  int32_t reserved;
+
+  /* V-trace outputs, each [T,B]; any may be NULL (VTraceFromLogitsReturns,
+     vtrace.py:37-40) */
+  float* vs;
+  float* pg_advantages;
+  float* log_rhos;
+  float* behaviour_action_log_probs;
+  float* target_action_log_probs;
+
+  /* gradients of the total loss; both NULL = forward only.
+     d_target_logits = (softmax - onehot(a))*pg_adv
+                       + entropy_cost * p*(log p + H)          [T,B,A]
+     d_values        = baseline_cost * (values - vs)            [T,B]   */
+  float* d_target_logits;
+  float* d_values;
+
+  /* losses, device memory; may be NULL (then no loss is computed).
+     losses[0]=policy-gradient, [1]=baseline (unweighted 0.5*sum sq),
+     [2]=entropy (unweighted, = -sum H), [3]=weighted total.            */
+  float* losses;      /* float[4]  */
+  double* losses_f64; /* double[4], may be NULL */
+} vtr_fused_params;
+
+/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A):
+   the per-tile loss partials of the deterministic two-stage reduction.
+   Returns 0 on invalid sizes. */
+size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A);
+
+/* The fused pass.  `workspace` must hold vtr_fused_workspace_bytes() bytes,
+   8-byte aligned; it is required only when p->losses is set. */
+int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* workspace,
+                              size_t workspace_bytes, void* stream);
+
+/* Second stage of the loss reduction on its own: sums `num_partials` rows of
+   double[3] in a fixed order.  (vtr_from_logits_fused_f32 calls this
+   internally; exposed for callers that shard a batch over several calls.)
+   Replaces the tf.reduce_sum calls at experiment.py:328,335,343. */
+int vtr_reduce_losses(const double* partials, int32_t num_partials,
+                      float baseline_cost, float entropy_cost, float* losses,
+                      double* losses_f64, void* stream);
+
+/*
+ * vtrace.from_importance_weights (vtrace.py:164-280) on its own.
+ * Shapes: values, rewards [T,B,C]; log_rhos, discounts [T,B,C] or [T,B,1];
+ * bootstrap_value [B,C]; C = 1 is the plain rank-2 case.  `bcast_mask` bit 0
+ * set = log_rhos has trailing size 1, bit 1 = discounts has trailing size 1
+ * (the broadcasting case of vtrace.py:178-180, vtrace_test.py:249-259).
+ * Outputs vs, pg_advantages [T,B,C].
+ */
+int vtr_from_importance_weights_f32(const float* log_rhos, const float* discounts,
+                                    const float* rewards, const float* values,
+                                    const float* bootstrap_value, int32_t T,
+                                    int32_t B, int32_t C, uint32_t bcast_mask,
+                                    float clip_rho_threshold,
+                                    float clip_pg_rho_threshold, uint32_t flags,
+                                    float* vs, float* pg_advantages, void* stream);
+
+/* vtrace.log_probs_from_logits_and_actions (vtrace.py:45-68): rows = T*B. */
+int vtr_log_probs_from_logits_and_actions_f32(const float* policy_logits,
+                                              const int32_t* actions,
+                                              int64_t rows, int32_t A,
+                                              float* log_probs, void* stream);
+
+/* Workspace for the three stand-alone loss helpers below, for `rows` rows
+   (or `rows` elements for the baseline loss). */
+size_t vtr_loss_workspace_bytes(int64_t rows);
+
+/* compute_policy_gradient_loss (experiment.py:338-343).
+   loss = sum_rows CE(logits, a) * advantages.  loss: device float[1]. */
+int vtr_policy_gradient_loss_f32(const float* logits, const int32_t* actions,
+                                 const float* advantages, int64_t rows, int32_t A,
+                                 float* loss, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+/* its backward: d_logits = grad_out * (softmax - onehot(a)) * advantages.
+   grad_out: device float[1] (the upstream scalar gradient). */
+int vtr_policy_gradient_loss_bwd_f32(const float* logits, const int32_t* actions,
+                                     const float* advantages,
+                                     const float* grad_out, int64_t rows,
+                                     int32_t A, float* d_logits, void* stream);
+
+/* compute_entropy_loss (experiment.py:331-335): loss = sum_rows sum_a p log p. */
+int vtr_entropy_loss_f32(const float* logits, int64_t rows, int32_t A, float* loss,
+                         void* workspace, size_t workspace_bytes, void* stream);
+/* its backward: d_logits = grad_out * p * (log p + H). */
+int vtr_entropy_loss_bwd_f32(const float* logits, const float* grad_out,
+                             int64_t rows, int32_t A, float* d_logits,
+                             void* stream);
+
+/* compute_baseline_loss (experiment.py:324-328): loss = 0.5 * sum adv^2. */
+int vtr_baseline_loss_f32(const float* advantages, int64_t n, float* loss,
+                          void* workspace, size_t workspace_bytes, void* stream);
+/* its backward: d_advantages = grad_out * advantages. */
+int vtr_baseline_loss_bwd_f32(const float* advantages, const float* grad_out,
+                              int64_t n, float* d_advantages, void* stream);
+
+/* x[i] *= *scale for i < n, skipped entirely when *scale == 1.  `scale` is a
+   device float[1].  Used to apply the upstream gradient of the total loss
+   (experiment.py:415) to the gradients the fused pass already produced,
+   without a host round trip to look at its value. */
+int vtr_scale_inplace_f32(float* x, const float* scale, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VTRACE_B200_H_ */

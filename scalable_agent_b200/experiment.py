@@ -1,0 +1,145 @@
+"""Drop-in for the loss helpers of the reference's `experiment.py`, on a B200.
+
+`compute_baseline_loss`, `compute_entropy_loss` and
+`compute_policy_gradient_loss` keep the reference's names, arguments and
+values (`/root/reference/experiment.py:324-343`) and are differentiable the
+way TF autodiff makes them (`experiment.py:415`).  `compute_vtrace_loss` is the
+fused form of the whole block `experiment.py:377-407`: one pass over the
+logits yields V-trace, the three losses, their weighted total and the
+gradients w.r.t. the learner's logits and baseline.
+
+Only the learner-loss path of `experiment.py` lives here; the TF1 training
+loop, agent network and environments are out of scope.
+"""
+import collections
+
+import torch
+
+from scalable_agent_b200 import _lib
+from scalable_agent_b200 import _ops
+from scalable_agent_b200 import vtrace
+from scalable_agent_b200.vtrace import _assert_rank, _device_of, _threshold, _to
+
+VTraceLossReturns = collections.namedtuple(
+    'VTraceLossReturns',
+    ['total_loss', 'policy_gradient_loss', 'baseline_loss', 'entropy_loss',
+     'vtrace_returns'])
+
+
+def compute_baseline_loss(advantages):
+  """0.5 * sum(advantages**2) (experiment.py:324-328)."""
+  dev = _device_of(advantages)
+  advantages = _to(advantages, torch.float32, dev)
+  return _ops.BaselineLoss.apply(advantages)
+
+
+def compute_entropy_loss(logits):
+  """-sum_t H(softmax(logits_t)) (experiment.py:331-335)."""
+  dev = _device_of(logits)
+  logits = _to(logits, torch.float32, dev)
+  return _ops.EntropyLoss.apply(logits)
+
+
+def compute_policy_gradient_loss(logits, actions, advantages):
+  """sum_t CE(logits_t, a_t) * stop_gradient(advantages_t) (experiment.py:338-343)."""
+  dev = _device_of(logits, actions, advantages)
+  logits = _to(logits, torch.float32, dev)
+  actions = _to(actions, torch.int32, dev)
+  advantages = _to(advantages, torch.float32, dev).detach()
+  if tuple(actions.shape) != tuple(logits.shape[:-1]):
+    raise ValueError('actions must have the shape of logits minus its last dim')
+  if tuple(advantages.shape) != tuple(actions.shape):
+    raise ValueError('advantages must have the shape of actions')
+  return _ops.PolicyGradientLoss.apply(logits, actions, advantages)
+
+
+def compute_vtrace_loss(
+    behaviour_policy_logits, target_policy_logits, actions, discounts,
+    rewards, values, bootstrap_value,
+    clip_rho_threshold=1.0, clip_pg_rho_threshold=1.0,
+    baseline_cost=.5, entropy_cost=.00025,
+    reward_clipping=None, done=None, discounting=.99,
+    return_aux=True, path='auto'):
+  """Fused learner loss: the block `experiment.py:377-407` in one pass.
+
+  Equivalent to
+
+      vtrace_returns = vtrace.from_logits(...)                       # :389-397
+      total  = compute_policy_gradient_loss(target_policy_logits, actions,
+                                            vtrace_returns.pg_advantages)
+      total += baseline_cost * compute_baseline_loss(vtrace_returns.vs - values)
+      total += entropy_cost * compute_entropy_loss(target_policy_logits)  # :401-407
+
+  but reads each input once, and `total_loss.backward()` costs no second pass
+  over the logits: the gradients w.r.t. `target_policy_logits` and `values`
+  are produced by the same kernel.  Defaults are the reference's flags
+  (`experiment.py:70-72`).
+
+  Args:
+    behaviour_policy_logits, target_policy_logits: float32 [T, B, NUM_ACTIONS].
+    actions: int32 [T, B].
+    discounts: float32 [T, B]; ignored (may be None) when `done` is given.
+    rewards, values: float32 [T, B].  bootstrap_value: float32 [B].
+    reward_clipping: None, 'abs_one' or 'soft_asymmetric' applied to
+      `rewards` inside the kernel (experiment.py:377-382).
+    done: optional bool [T, B]; discounts = (~done) * discounting (:384).
+    return_aux: also materialise log_rhos and the two action log-prob fields.
+    path: 'auto', 'column' or 'scan' (kernel choice).
+
+  Returns:
+    VTraceLossReturns(total_loss, policy_gradient_loss, baseline_loss,
+    entropy_loss, vtrace_returns).  Only `total_loss` is differentiable; the
+    component losses are reported unweighted, for logging.
+  """
+  dev = _device_of(behaviour_policy_logits, target_policy_logits, actions,
+                   discounts, rewards, values, bootstrap_value)
+  behaviour_policy_logits = _to(behaviour_policy_logits, torch.float32, dev)
+  target_policy_logits = _to(target_policy_logits, torch.float32, dev)
+  actions = _to(actions, torch.int32, dev)
+  rewards = _to(rewards, torch.float32, dev)
+  values = _to(values, torch.float32, dev)
+  bootstrap_value = _to(bootstrap_value, torch.float32, dev)
+  if done is not None:
+    done = _to(done, torch.bool, dev).view(torch.uint8)
+    discounts = torch.empty(0, dtype=torch.float32, device=dev)
+  elif discounts is None:
+    raise ValueError('one of discounts / done must be given')
+  else:
+    discounts = _to(discounts, torch.float32, dev)
+  if reward_clipping not in _lib.REWARD_CLIP_MODES:
+    raise ValueError('unknown reward_clipping %r' % (reward_clipping,))
+  if path not in _lib.PATHS:
+    raise ValueError('unknown path %r' % (path,))
+  clip_rho_threshold = _threshold(clip_rho_threshold, 'clip_rho_threshold')
+  clip_pg_rho_threshold = _threshold(clip_pg_rho_threshold,
+                                     'clip_pg_rho_threshold')
+
+  _assert_rank(behaviour_policy_logits, 3, 'behaviour_policy_logits')
+  _assert_rank(target_policy_logits, 3, 'target_policy_logits')
+  T, B, A = target_policy_logits.shape
+  if tuple(behaviour_policy_logits.shape) != (T, B, A):
+    raise ValueError('behaviour and target logits differ in shape')
+  per_step = [(actions, 'actions'), (rewards, 'rewards'), (values, 'values')]
+  per_step.append((done, 'done') if done is not None
+                  else (discounts, 'discounts'))
+  for t, n in per_step:
+    _assert_rank(t, 2, n)
+    if tuple(t.shape) != (T, B):
+      raise ValueError('%s must have shape [T, B] = %s' % (n, (T, B)))
+  _assert_rank(bootstrap_value, 1, 'bootstrap_value')
+  if tuple(bootstrap_value.shape) != (B,):
+    raise ValueError('bootstrap_value must have shape [B]')
+
+  total, losses, vs, pg, log_rhos, b_lp, t_lp = _ops.FusedLoss.apply(
+      behaviour_policy_logits, target_policy_logits, actions, discounts,
+      rewards, values, bootstrap_value, done, clip_rho_threshold,
+      clip_pg_rho_threshold, float(baseline_cost), float(entropy_cost),
+      float(discounting), _lib.REWARD_CLIP_MODES[reward_clipping],
+      bool(return_aux), _lib.PATHS[path])
+  aux = (log_rhos, b_lp, t_lp) if return_aux else (None, None, None)
+  return VTraceLossReturns(
+      total_loss=total, policy_gradient_loss=losses[0],
+      baseline_loss=losses[1], entropy_loss=losses[2],
+      vtrace_returns=vtrace.VTraceFromLogitsReturns(
+          vs=vs, pg_advantages=pg, log_rhos=aux[0],
+          behaviour_action_log_probs=aux[1], target_action_log_probs=aux[2]))

@@ -1,0 +1,416 @@
+"""GPU parity tests: the CUDA path (through the Python API -> ctypes -> C ABI)
+against the float64 oracle and the golden fixtures.
+
+Tolerance (BASELINE.json north_star):
+    |x - ref| <= 1e-5 * max(1, |ref|)   elementwise and for the loss scalars,
+    bitwise equality between two runs on the same inputs.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import vtrace_oracle as oracle
+from tests.conftest import Golden, assert_close
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+@pytest.fixture(scope='module')
+def api():
+  assert torch.cuda.is_available(), 'GPU tests need a CUDA device'
+  from scalable_agent_b200 import experiment, vtrace
+  return vtrace, experiment
+
+
+def _dev(x):
+  return torch.as_tensor(x).cuda()
+
+
+def _np(x):
+  return x.detach().cpu().numpy()
+
+
+FUSED_KEYS = ('behaviour_policy_logits', 'target_policy_logits', 'actions',
+              'discounts', 'rewards', 'values', 'bootstrap_value')
+
+
+def _run_fused(experiment, inp, requires_grad=True, **kw):
+  args = {k: _dev(inp[k]) for k in FUSED_KEYS}
+  if requires_grad:
+    args['target_policy_logits'].requires_grad_(True)
+    args['values'].requires_grad_(True)
+  out = experiment.compute_vtrace_loss(**args, **kw)
+  return args, out
+
+
+def _check_fused(experiment, inp, crho=1.0, cpg=1.0, bc=0.5, ec=0.00025,
+                 path='auto', tol=TOL, **kw):
+  ref = oracle.fused_vtrace_loss(
+      *[inp[k] for k in FUSED_KEYS], crho, cpg, bc, ec,
+      reward_clipping=kw.get('reward_clipping'), done=kw.get('done_np'),
+      discounting=kw.get('discounting', 0.99))
+  call_kw = dict(clip_rho_threshold=crho, clip_pg_rho_threshold=cpg,
+                 baseline_cost=bc, entropy_cost=ec, path=path)
+  if 'reward_clipping' in kw:
+    call_kw['reward_clipping'] = kw['reward_clipping']
+  if 'done_np' in kw:
+    call_kw['done'] = _dev(kw['done_np'])
+    call_kw['discounting'] = kw.get('discounting', 0.99)
+  args, out = _run_fused(experiment, inp, **call_kw)
+  vt = out.vtrace_returns
+  assert_close(_np(vt.vs), ref.vs, tol, 'vs')
+  assert_close(_np(vt.pg_advantages), ref.pg_advantages, tol, 'pg_advantages')
+  assert_close(_np(vt.log_rhos), ref.log_rhos, tol, 'log_rhos')
+  assert_close(_np(vt.behaviour_action_log_probs),
+               ref.behaviour_action_log_probs, tol, 'b_lp')
+  assert_close(_np(vt.target_action_log_probs), ref.target_action_log_probs,
+               tol, 't_lp')
+  assert_close(_np(out.policy_gradient_loss), ref.pg_loss, tol, 'pg_loss')
+  assert_close(_np(out.baseline_loss), ref.baseline_loss, tol, 'baseline_loss')
+  assert_close(_np(out.entropy_loss), ref.entropy_loss, tol, 'entropy_loss')
+  assert_close(_np(out.total_loss), ref.total_loss, tol, 'total_loss')
+  out.total_loss.backward()
+  assert_close(_np(args['target_policy_logits'].grad), ref.d_target_logits,
+               tol, 'd_target_logits')
+  assert_close(_np(args['values'].grad), ref.d_values, tol, 'd_values')
+  return out
+
+
+# ---------------------------------------------------------------------------
+# The reference's own tests (vtrace_test.py), against the frozen expectations
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize('case', ['test_log_probs_B1', 'test_log_probs_B2'])
+def test_log_probs_from_logits_and_actions(api, golden, case):
+  vtrace, _ = api
+  c = golden.case(case)
+  lp = vtrace.log_probs_from_logits_and_actions(c['policy_logits'], c['actions'])
+  assert lp.dtype == torch.float32 and lp.is_cuda
+  # the reference's tolerance: assertAllClose default 1e-6 (vtrace_test.py:115)
+  np.testing.assert_allclose(_np(lp), c['log_probs'], rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize('case', ['test_vtrace_B1', 'test_vtrace_B5'])
+def test_vtrace(api, golden, case):
+  vtrace, _ = api
+  c = golden.case(case)
+  out = vtrace.from_importance_weights(
+      log_rhos=c['log_rhos'], discounts=c['discounts'], rewards=c['rewards'],
+      values=c['values'], bootstrap_value=c['bootstrap_value'],
+      clip_rho_threshold=float(c['clip_rho_threshold']),
+      clip_pg_rho_threshold=float(c['clip_pg_rho_threshold']))
+  assert isinstance(out, vtrace.VTraceReturns)
+  assert_close(_np(out.vs), c['vs_f64'], TOL, 'vs')
+  assert_close(_np(out.pg_advantages), c['pg_advantages_f64'], TOL, 'pg')
+  # and the reference's own float32 expectation at its tolerance (:154-156)
+  np.testing.assert_allclose(_np(out.vs), c['vs'], rtol=1e-6, atol=1e-6)
+  np.testing.assert_allclose(_np(out.pg_advantages), c['pg_advantages'],
+                             rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize('case', ['test_vtrace_from_logits_B1',
+                                  'test_vtrace_from_logits_B2'])
+def test_vtrace_from_logits(api, golden, case):
+  """vtrace_test.py:158-247 (config 1): from_logits == from_importance_weights
+  fed the separately computed log-probs; the three extra fields match."""
+  vtrace, _ = api
+  c = golden.case(case)
+  keys = ('behaviour_policy_logits', 'target_policy_logits', 'actions',
+          'discounts', 'rewards', 'values', 'bootstrap_value')
+  out = vtrace.from_logits(clip_rho_threshold=None, clip_pg_rho_threshold=None,
+                           **{k: c[k] for k in keys})
+  assert isinstance(out, vtrace.VTraceFromLogitsReturns)
+  assert out._fields == ('vs', 'pg_advantages', 'log_rhos',
+                         'behaviour_action_log_probs',
+                         'target_action_log_probs')
+  t_lp = vtrace.log_probs_from_logits_and_actions(c['target_policy_logits'],
+                                                  c['actions'])
+  b_lp = vtrace.log_probs_from_logits_and_actions(c['behaviour_policy_logits'],
+                                                  c['actions'])
+  from_iw = vtrace.from_importance_weights(
+      log_rhos=t_lp - b_lp, discounts=c['discounts'], rewards=c['rewards'],
+      values=c['values'], bootstrap_value=c['bootstrap_value'],
+      clip_rho_threshold=None, clip_pg_rho_threshold=None)
+  kw = dict(rtol=1e-6, atol=1e-6)
+  np.testing.assert_allclose(_np(from_iw.vs), _np(out.vs), **kw)
+  np.testing.assert_allclose(_np(from_iw.pg_advantages),
+                             _np(out.pg_advantages), **kw)
+  np.testing.assert_allclose(_np(b_lp), _np(out.behaviour_action_log_probs), **kw)
+  np.testing.assert_allclose(_np(t_lp), _np(out.target_action_log_probs), **kw)
+  np.testing.assert_allclose(_np(t_lp - b_lp), _np(out.log_rhos), **kw)
+  for f in out._fields:
+    assert_close(_np(getattr(out, f)), c[f], TOL, f)
+  assert not out.vs.requires_grad and not out.pg_advantages.requires_grad
+
+
+def test_higher_rank_inputs_for_importance_weights(api):
+  """vtrace_test.py:249-259."""
+  vtrace, _ = api
+  T, B, C = 6, 5, 42
+  rng = np.random.default_rng(0)
+  log_rhos = rng.standard_normal((T, B, 1)).astype(np.float32)
+  discounts = np.full((T, B, 1), 0.9, np.float32)
+  rewards = rng.standard_normal((T, B, C)).astype(np.float32)
+  values = rng.standard_normal((T, B, C)).astype(np.float32)
+  bootstrap = rng.standard_normal((B, C)).astype(np.float32)
+  out = vtrace.from_importance_weights(log_rhos, discounts, rewards, values,
+                                       bootstrap)
+  assert out.vs.shape[-1] == 42 and tuple(out.vs.shape) == (T, B, C)
+  ref = oracle.from_importance_weights(log_rhos, discounts, rewards, values,
+                                       bootstrap)
+  assert_close(_np(out.vs), ref.vs, TOL, 'vs')
+  assert_close(_np(out.pg_advantages), ref.pg_advantages, TOL, 'pg')
+  # full-width log_rhos/discounts too
+  log_rhos_c = np.broadcast_to(log_rhos, (T, B, C)).copy()
+  out2 = vtrace.from_importance_weights(log_rhos_c, discounts, rewards, values,
+                                        bootstrap, None, None)
+  ref2 = oracle.from_importance_weights(log_rhos_c, discounts, rewards, values,
+                                        bootstrap, None, None)
+  assert_close(_np(out2.vs), ref2.vs, TOL, 'vs')
+  assert_close(_np(out2.pg_advantages), ref2.pg_advantages, TOL, 'pg')
+
+
+def test_inconsistent_rank_inputs_for_importance_weights(api):
+  """vtrace_test.py:261-272."""
+  vtrace, _ = api
+  z = lambda *s: np.zeros(s, np.float32)
+  with pytest.raises(ValueError, match='must have rank 2'):
+    vtrace.from_importance_weights(z(4, 3, 1), z(4, 3, 1), z(4, 3, 42),
+                                   z(4, 3, 42), z(3))
+
+
+# ---------------------------------------------------------------------------
+# Fused forward+backward against the oracle
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize('case', [
+    'synthetic_T100_B32_A9', 'synthetic_T20_B96_A18',
+    'synthetic_T100_B40_A18_noclip', 'synthetic_T33_B7_A5_clip'])
+def test_from_logits_vs_reference_ground_truth(api, golden, case):
+  vtrace, _ = api
+  c = golden.case(case)
+  crho = Golden.threshold(c['clip_rho_threshold'])
+  cpg = Golden.threshold(c['clip_pg_rho_threshold'])
+  out = vtrace.from_logits(*[c[k] for k in FUSED_KEYS], crho, cpg)
+  for f in out._fields:
+    assert_close(_np(getattr(out, f)), c[f], TOL, f)
+
+
+@pytest.mark.parametrize('T,B,A', [
+    (5, 2, 3),        # config 1 (plumbing)
+    (100, 32, 9),     # config 2 (DMLab single level)
+    (20, 512, 18),    # short unroll
+    (1, 1, 1), (1, 33, 2), (2, 31, 4), (3, 64, 6),
+    (7, 65, 5), (40, 37, 7), (9, 100, 32), (6, 34, 100), (4, 3, 256),
+    (50, 130, 9), (100, 70, 18),
+])
+@pytest.mark.parametrize('path', ['column'])
+def test_fused_matches_oracle(api, T, B, A, path):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T * 1000 + B + A)
+  _check_fused(experiment, inp, path=path)
+
+
+@pytest.mark.parametrize('crho,cpg', [(None, None), (3.7, 2.2), (1.0, None),
+                                      (0.0, 0.0)])
+def test_fused_thresholds(api, crho, cpg):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(30, 48, 9, seed=9)
+  _check_fused(experiment, inp, crho=crho, cpg=cpg, ec=0.0033391318945337044)
+
+
+def test_fused_reward_clipping_and_done(api):
+  """experiment.py:377-384 fused into the prologue."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(25, 66, 9, seed=21, reward_clipping=None)
+  inp['rewards'] = inp['raw_rewards']
+  for mode in ('abs_one', 'soft_asymmetric'):
+    _check_fused(experiment, inp, reward_clipping=mode, done_np=inp['done'],
+                 discounting=0.97)
+
+
+def test_config3_dmlab30_large(api):
+  """BASELINE.json config 3: T=100, B=2048, A=9, soft_asymmetric."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(100, 2048, 9, seed=3,
+                                reward_clipping='soft_asymmetric')
+  _check_fused(experiment, inp, ec=0.0033391318945337044)
+
+
+def test_config4_short_unroll(api):
+  """BASELINE.json config 4: T=20, B=16384, A=18."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(20, 16384, 18, seed=4)
+  _check_fused(experiment, inp)
+
+
+def test_target_shape_full_size(api):
+  """The headline shape T=100, B=32768, A=18 against the oracle, plus the
+  size-independent properties: run-to-run bitwise determinism and column
+  independence (a B-slice computed alone gives the same bits)."""
+  _, experiment = api
+  T, B, A = 100, 32768, 18
+  inp = oracle.synthetic_inputs(T, B, A, seed=1)
+  out = _check_fused(experiment, inp)
+  args, out2 = _run_fused(experiment, inp)
+  assert torch.equal(out.vtrace_returns.vs, out2.vtrace_returns.vs)
+  assert torch.equal(out.total_loss, out2.total_loss)
+  lo, hi = 4096, 4096 + 640
+  sl = {k: (inp[k][:, lo:hi] if inp[k].ndim >= 2 else inp[k][lo:hi]).copy()
+        for k in FUSED_KEYS}
+  _, out_sl = _run_fused(experiment, sl)
+  assert torch.equal(out_sl.vtrace_returns.vs, out.vtrace_returns.vs[:, lo:hi])
+  assert torch.equal(out_sl.vtrace_returns.pg_advantages,
+                     out.vtrace_returns.pg_advantages[:, lo:hi])
+
+
+def test_bitwise_determinism(api):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(100, 1000, 18, seed=5)
+  results = []
+  for _ in range(3):
+    args, out = _run_fused(experiment, inp)
+    out.total_loss.backward()
+    results.append((out, args['target_policy_logits'].grad.clone(),
+                    args['values'].grad.clone()))
+  for out, dl, dv in results[1:]:
+    assert torch.equal(out.total_loss, results[0][0].total_loss)
+    assert torch.equal(out.policy_gradient_loss, results[0][0].policy_gradient_loss)
+    assert torch.equal(out.vtrace_returns.vs, results[0][0].vtrace_returns.vs)
+    assert torch.equal(dl, results[0][1]) and torch.equal(dv, results[0][2])
+
+
+def test_unaligned_views_take_the_generic_loader(api):
+  """Rows that are not 16-byte aligned (odd B*A, offset base pointers)."""
+  _, experiment = api
+  T, B, A = 12, 35, 9            # B*A = 315: rows not 16-byte multiples
+  inp = oracle.synthetic_inputs(T, B, A, seed=8)
+  _check_fused(experiment, inp)
+  # misaligned base pointer: a contiguous tensor carved at a 4-byte offset
+  T, B, A = 10, 64, 18
+  inp = oracle.synthetic_inputs(T, B, A, seed=12)
+  from scalable_agent_b200 import vtrace
+  def shifted(x):
+    flat = torch.empty(x.size + 1, dtype=torch.float32, device='cuda')
+    view = flat[1:].view(x.shape)
+    view.copy_(torch.from_numpy(x))
+    return view
+  out = vtrace.from_logits(
+      shifted(inp['behaviour_policy_logits']),
+      shifted(inp['target_policy_logits']), inp['actions'], inp['discounts'],
+      inp['rewards'], inp['values'], inp['bootstrap_value'])
+  ref = oracle.from_logits(*[inp[k] for k in FUSED_KEYS])
+  for f in out._fields:
+    assert_close(_np(getattr(out, f)), getattr(ref, f), TOL, f)
+
+
+def test_upstream_gradient_scaling(api):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(10, 40, 9, seed=2)
+  ref = oracle.fused_vtrace_loss(*[inp[k] for k in FUSED_KEYS])
+  args, out = _run_fused(experiment, inp)
+  (out.total_loss * 0.25).backward()
+  assert_close(_np(args['target_policy_logits'].grad),
+               0.25 * ref.d_target_logits, TOL, 'scaled d_logits')
+  assert_close(_np(args['values'].grad), 0.25 * ref.d_values, TOL,
+               'scaled d_values')
+
+
+# ---------------------------------------------------------------------------
+# The stand-alone helpers (experiment.py:324-343) and their composition
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize('T,B,A', [(5, 2, 3), (100, 32, 9), (20, 300, 18),
+                                   (3, 5, 130)])
+def test_loss_helpers_compose_like_the_reference(api, T, B, A):
+  """experiment.py:389-407 written with the individual drop-in functions."""
+  vtrace, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T + A)
+  bc, ec = 0.5, 0.01
+  ref = oracle.fused_vtrace_loss(*[inp[k] for k in FUSED_KEYS], 1.0, 1.0, bc, ec)
+  logits = _dev(inp['target_policy_logits']).requires_grad_(True)
+  baseline = _dev(inp['values']).requires_grad_(True)
+  actions = _dev(inp['actions'])
+  vtrace_returns = vtrace.from_logits(
+      behaviour_policy_logits=_dev(inp['behaviour_policy_logits']),
+      target_policy_logits=logits, actions=actions,
+      discounts=_dev(inp['discounts']), rewards=_dev(inp['rewards']),
+      values=baseline, bootstrap_value=_dev(inp['bootstrap_value']))
+  pg_loss = experiment.compute_policy_gradient_loss(
+      logits, actions, vtrace_returns.pg_advantages)
+  bl_loss = experiment.compute_baseline_loss(vtrace_returns.vs - baseline)
+  ent_loss = experiment.compute_entropy_loss(logits)
+  total = pg_loss + bc * bl_loss + ec * ent_loss
+  assert_close(_np(pg_loss), ref.pg_loss, TOL, 'pg_loss')
+  assert_close(_np(bl_loss), ref.baseline_loss, TOL, 'baseline_loss')
+  assert_close(_np(ent_loss), ref.entropy_loss, TOL, 'entropy_loss')
+  total.backward()
+  assert_close(_np(logits.grad), ref.d_target_logits, TOL, 'd_logits')
+  assert_close(_np(baseline.grad), ref.d_values, TOL, 'd_values')
+
+
+def test_log_probs_and_aux_outputs_are_differentiable(api):
+  """vtrace.py:156-161: log_rhos and the log-prob fields are not stop_gradient."""
+  vtrace, _ = api
+  inp = oracle.synthetic_inputs(6, 10, 7, seed=6)
+  t64 = torch.tensor(inp['target_policy_logits'], dtype=torch.float64,
+                     requires_grad=True)
+  b64 = torch.tensor(inp['behaviour_policy_logits'], dtype=torch.float64,
+                     requires_grad=True)
+  idx = torch.tensor(inp['actions'].astype(np.int64))[..., None]
+  w = torch.tensor(np.random.default_rng(0).standard_normal((6, 10)))
+  t_lp = torch.log_softmax(t64, -1).gather(-1, idx)[..., 0]
+  b_lp = torch.log_softmax(b64, -1).gather(-1, idx)[..., 0]
+  ((t_lp - b_lp) * w + 2 * t_lp - 3 * b_lp).sum().backward()
+
+  target = _dev(inp['target_policy_logits']).requires_grad_(True)
+  behaviour = _dev(inp['behaviour_policy_logits']).requires_grad_(True)
+  out = vtrace.from_logits(behaviour, target, inp['actions'], inp['discounts'],
+                           inp['rewards'], inp['values'], inp['bootstrap_value'])
+  wd = w.float().cuda()
+  (out.log_rhos * wd + 2 * out.target_action_log_probs
+   - 3 * out.behaviour_action_log_probs).sum().backward()
+  assert_close(_np(target.grad), t64.grad.numpy(), TOL, 'd target')
+  assert_close(_np(behaviour.grad), b64.grad.numpy(), TOL, 'd behaviour')
+
+  logits = _dev(inp['target_policy_logits']).requires_grad_(True)
+  lp = vtrace.log_probs_from_logits_and_actions(logits, inp['actions'])
+  (lp * wd).sum().backward()
+  t64.grad = None
+  (torch.log_softmax(t64, -1).gather(-1, idx)[..., 0] * w).sum().backward()
+  assert_close(_np(logits.grad), t64.grad.numpy(), TOL, 'd log_probs')
+
+
+def test_c_abi_direct_call(api):
+  """Straight through ctypes, no torch op layer: raw pointers in, codes out."""
+  import ctypes
+  from scalable_agent_b200 import _lib
+  lib = _lib.load()
+  T, B, A = 8, 50, 9
+  inp = oracle.synthetic_inputs(T, B, A, seed=13)
+  d = {k: _dev(inp[k]) for k in FUSED_KEYS}
+  vs = torch.empty(T, B, device='cuda')
+  pg = torch.empty(T, B, device='cuda')
+  losses = torch.empty(4, device='cuda')
+  losses64 = torch.empty(4, device='cuda', dtype=torch.float64)
+  p = _lib.FusedParams()
+  p.T, p.B, p.A = T, B, A
+  for k in FUSED_KEYS:
+    setattr(p, k, d[k].data_ptr())
+  p.clip_rho_threshold = p.clip_pg_rho_threshold = 1.0
+  p.baseline_cost, p.entropy_cost = 0.5, 0.00025
+  p.vs, p.pg_advantages = vs.data_ptr(), pg.data_ptr()
+  p.losses, p.losses_f64 = losses.data_ptr(), losses64.data_ptr()
+  nbytes = lib.vtr_fused_workspace_bytes(T, B, A)
+  ws = torch.empty(nbytes // 8, dtype=torch.float64, device='cuda')
+  stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+  # too-small workspace is refused before any launch
+  assert lib.vtr_from_logits_fused_f32(ctypes.byref(p), ws.data_ptr(), 8, stream) == -3
+  rc = lib.vtr_from_logits_fused_f32(ctypes.byref(p), ws.data_ptr(), nbytes, stream)
+  assert rc == 0, _lib.last_error()
+  torch.cuda.synchronize()
+  ref = oracle.fused_vtrace_loss(*[inp[k] for k in FUSED_KEYS])
+  assert_close(_np(vs), ref.vs, TOL, 'vs')
+  assert_close(_np(pg), ref.pg_advantages, TOL, 'pg')
+  want = [ref.pg_loss, ref.baseline_loss, ref.entropy_loss, ref.total_loss]
+  assert_close(_np(losses), want, TOL, 'losses')
+  assert_close(_np(losses64), want, TOL, 'losses_f64')
