@@ -1,0 +1,67 @@
+"""Batch-sharded use of the path across the GPUs of one box.
+
+V-trace columns are independent (`/root/reference/vtrace.py:250-262` works
+elementwise over `[B]`) and the losses are plain sums over (t, b)
+(`experiment.py:328,335,343`), so a data-parallel learner gives each rank its
+own contiguous `[T, B/N, ...]` tensors and runs the same kernels on them.  The
+only exchange is the loss scalars: they are all-gathered and summed in rank
+order, so the global loss is bitwise reproducible whatever algorithm NCCL
+picks.  Gradients w.r.t. logits and values are per-sample and stay local.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(B, world_size, rank):
+  """[lo, hi) of the batch columns rank `rank` owns (contiguous, balanced)."""
+  if not 0 <= rank < world_size:
+    raise ValueError('rank %d outside world of %d' % (rank, world_size))
+  base, extra = divmod(B, world_size)
+  lo = rank * base + min(rank, extra)
+  return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_time_major(x, world_size, rank, batch_dim=1):
+  """The rank's contiguous copy of its columns of a time-major tensor."""
+  lo, hi = shard_bounds(x.shape[batch_dim], world_size, rank)
+  return x.narrow(batch_dim, lo, hi - lo).contiguous()
+
+
+def all_reduce_losses(local_losses, group=None):
+  """Sum a small loss vector over ranks, deterministically.
+
+  Args:
+    local_losses: tensor [k] (e.g. the 4 loss scalars of the fused pass) on
+      this rank's device.
+  Returns:
+    tensor [k]: sum over ranks, accumulated in float64 in rank order,
+    returned in `local_losses.dtype`.  Every rank gets identical bits.
+  """
+  if not dist.is_available() or not dist.is_initialized():
+    return local_losses.clone()
+  world = dist.get_world_size(group)
+  if world == 1:
+    return local_losses.clone()
+  flat = local_losses.detach().reshape(-1).contiguous()
+  gathered = torch.empty(world * flat.numel(), dtype=flat.dtype,
+                         device=flat.device)
+  dist.all_gather_into_tensor(gathered, flat, group=group)
+  total = torch.zeros(flat.numel(), dtype=torch.float64, device=flat.device)
+  for r in range(world):            # fixed order: rank 0, 1, ...
+    total += gathered[r * flat.numel():(r + 1) * flat.numel()].double()
+  return total.to(local_losses.dtype).reshape(local_losses.shape)
+
+
+def compute_vtrace_loss_sharded(*args, group=None, **kwargs):
+  """`experiment.compute_vtrace_loss` on this rank's shard + global losses.
+
+  Returns (local VTraceLossReturns, global_losses[4]) where global_losses =
+  [total, policy_gradient, baseline, entropy] summed over ranks.  Call
+  `.backward()` on the local `total_loss`: d(global total)/d(local logits) is
+  exactly the local gradient, because shards share no terms.
+  """
+  from scalable_agent_b200 import experiment
+  out = experiment.compute_vtrace_loss(*args, **kwargs)
+  local = torch.stack([out.total_loss.detach(), out.policy_gradient_loss,
+                       out.baseline_loss, out.entropy_loss])
+  return out, all_reduce_losses(local, group=group)
