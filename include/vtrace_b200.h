@@ -139,6 +139,30 @@ size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A);
 int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* workspace,
                               size_t workspace_bytes, void* stream);
 
+/* Most batch columns the allocation-free entry point below accepts. */
+#define VTR_NOALLOC_MAX_B 262144
+
+/* No counterpart in the reference: the same fused pass for callers that cannot
+   allocate device memory, and so cannot supply the workspace above -- an op
+   inside a framework that hands it inputs and pre-declared outputs but no
+   temporary allocator, or a learner running in a process where cudaMalloc is
+   forbidden after start-up because the memory pool owns the whole GPU and a
+   cudaMalloc would fail or stall the other streams by synchronising the
+   device.  The tile partials go to a 192 KiB array built into the library
+   (every GPU that loads the library holds it until the process exits); the
+   caller still passes all inputs and outputs in `p`.  Results are identical to
+   vtr_from_logits_fused_f32.
+   - p->B must be <= VTR_NOALLOC_MAX_B, else VTR_ERR_UNSUPPORTED.
+   - No cudaMalloc/cudaFree or allocating library routine is called.
+   - The first call on each device looks the array's address up (with that
+     device current); make that first call before any stream capture.
+   - All calls on a device share the one array, which keeps the previous call's
+     contents.  Nothing needs zeroing (each call rewrites every slot it reads),
+     but two calls that overlap on the GPU -- different streams, no ordering
+     between them -- race on it and corrupt each other's losses.  Serialise
+     them, or use the workspace variant. */
+int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void* stream);
+
 /* Second stage of the loss reduction on its own: sums `num_partials` rows of
    double[3] in a fixed order.  (vtr_from_logits_fused_f32 calls this
    internally; exposed for callers that shard a batch over several calls.)

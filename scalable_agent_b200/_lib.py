@@ -67,6 +67,8 @@ SIGNATURES = {
     'vtr_fused_workspace_bytes': (_SZ, [_I32, _I32, _I32]),
     'vtr_from_logits_fused_f32':
         (ctypes.c_int, [ctypes.POINTER(FusedParams), _P, _SZ, _P]),
+    'vtr_from_logits_fused_noalloc_f32':
+        (ctypes.c_int, [ctypes.POINTER(FusedParams), _P]),
     'vtr_reduce_losses': (ctypes.c_int, [_P, _I32, _F, _F, _P, _P, _P]),
     'vtr_from_importance_weights_f32':
         (ctypes.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _U32, _F, _F,

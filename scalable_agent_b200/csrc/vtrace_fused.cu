@@ -526,3 +526,61 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   }
   return VTR_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of the fused pass.
+//
+// Some callers of this library have no way to hand over a workspace: a
+// framework op whose outputs were all declared up front and which gets no
+// temporary allocator, or a learner thread inside a process whose device
+// memory was carved up at start-up and where cudaMalloc is banned afterwards
+// (it can fail once the pool owns the GPU, and it synchronises the device,
+// stalling the inference streams that share it).  For them the tile partials
+// of the two-stage loss reduction live in the fixed array below instead of a
+// caller buffer.  Every GPU that loads the library carries these 192 KiB until
+// the process exits, whether or not this entry point is ever called.
+// ---------------------------------------------------------------------------
+#include <mutex>
+
+namespace vtr {
+
+constexpr int kNoAllocMaxTiles = VTR_NOALLOC_MAX_B / kColumnsPerTile;
+static __device__ __align__(256) double g_noalloc_partials[kNoAllocMaxTiles * 3];
+
+// In host code `g_noalloc_partials` only names the symbol; the address the
+// kernels can use is per device and comes from cudaGetSymbolAddress, asked
+// once per device with that device current.
+static int noalloc_scratch(double** out) {
+  constexpr int kMaxDevices = 64;
+  static double* cache[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = 0;
+  VTR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(VTR_ERR_UNSUPPORTED, "device index %d", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cache[dev]) {
+    void* ptr = nullptr;
+    VTR_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_noalloc_partials));
+    if (!ptr) return fail(VTR_ERR_WORKSPACE, "cudaGetSymbolAddress returned a null scratch address");
+    cache[dev] = static_cast<double*>(ptr);
+  }
+  *out = cache[dev];
+  return VTR_OK;
+}
+
+}  // namespace vtr
+
+extern "C" int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void* stream) {
+  if (!p) return vtr::fail(VTR_ERR_INVALID_ARGUMENT, "params is NULL");
+  if (p->B > VTR_NOALLOC_MAX_B)
+    return vtr::fail(VTR_ERR_UNSUPPORTED,
+                     "vtr_from_logits_fused_noalloc_f32: B=%d is above VTR_NOALLOC_MAX_B=%d, the most "
+                     "the built-in scratch holds; use vtr_from_logits_fused_f32 with your own workspace",
+                     p->B, VTR_NOALLOC_MAX_B);
+  double* scratch = nullptr;
+  if (int rc = vtr::noalloc_scratch(&scratch)) return rc;
+  // Nothing in the scratch has to start at zero: the first stage writes the
+  // partial of every tile the second stage reads, so whatever an earlier call
+  // left behind is overwritten or never looked at.
+  return vtr_from_logits_fused_f32(p, scratch, sizeof(double) * 3 * vtr::kNoAllocMaxTiles, stream);
+}
