@@ -8,7 +8,9 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'lib', 'libvtrace_b200.so')
+# VTRACE_B200_LIB points at another build of the same ABI (A/B experiments).
+LIB_PATH = os.environ.get('VTRACE_B200_LIB') or os.path.join(
+    _HERE, 'lib', 'libvtrace_b200.so')
 
 VTR_OK = 0
 VTR_MAX_ACTIONS = 256

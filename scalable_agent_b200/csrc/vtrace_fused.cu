@@ -4,29 +4,34 @@
 // (experiment.py:324-343), the weighted total (experiment.py:401-407) and the
 // autodiff backward of that total (experiment.py:415).
 //
-// K1 "column" kernel (this file): one warp owns 32 adjacent batch columns and
-// walks time from T-1 down to 0, one lane per column, so the reverse
-// recurrence acc_t = delta_t + gamma_t c_t acc_{t+1} (vtrace.py:250-262) and
-// vs_{t+1} (vtrace.py:268-269) are live registers.  For one time step the 32
+// K1 (this file).  A tile is 32 adjacent batch columns, one lane per column,
+// walked from t = T-1 down to 0 so that the reverse recurrence
+// acc_t = delta_t + gamma_t c_t acc_{t+1} (vtrace.py:250-262) and vs_{t+1}
+// (vtrace.py:268-269) are carried, not recomputed.  For one time step the 32
 // columns' logits are ONE contiguous run of 32*A floats in the time-major
-// [T,B,A] layout; a ring of `depth` stages in shared memory is kept full by
-// TMA bulk copies (cp.async.bulk -> mbarrier complete_tx) for both logits
-// tensors plus 4-byte cp.async for the four [T,B] operands, all landing on the
-// same mbarrier.  d_target_logits is staged in shared memory and leaves with a
-// TMA bulk store.  Losses accumulate per lane in double, are reduced over the
-// warp with a fixed shuffle tree and written as one partial per tile; K3
-// (reduce_losses_kernel) sums the partials in a fixed order.  No atomics.
+// [T,B,A] layout; a ring of `depth` slots in shared memory is kept full by TMA
+// bulk copies (cp.async.bulk -> mbarrier complete_tx) for both logits tensors
+// plus 4-byte cp.async for the four [T,B] operands, all landing on the slot's
+// one mbarrier.  d_target_logits rows are staged in shared memory and leave
+// with TMA bulk stores.  Two shells run the same arithmetic (vtrace_math.cuh):
+//   K1a fused_column_kernel  one warp per tile, deepest ring   (>= 7 tiles/SM)
+//   K1b fused_relay_kernel   W warps per tile relaying the carry (< 7 tiles/SM)
+// Losses accumulate per lane in double, are reduced with a fixed shuffle tree
+// and written as one partial per tile; K3 (reduce_losses_kernel) sums the
+// partials in a fixed order.  No atomics.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.h"
 #include "ptx.cuh"
+#include "vtrace_math.cuh"
 
 namespace vtr {
 
 struct FusedArgs {
   int T, B, A;
-  int depth;         // ring stages
-  int stage_floats;  // floats per stage: 2*32*A logits + 4*32 per-step operands
+  int depth;        // ring slots
+  int slot_floats;  // floats per ring slot: 2*32*A logits + 4*32 per-step operands
   uint32_t flags;
   int reward_clip_mode;
   int tma_in_ok;   // logits rows are 16-byte aligned for every t and tile
@@ -51,8 +56,10 @@ struct FusedArgs {
 };
 
 constexpr int kColumnsPerTile = 32;
-constexpr int kBarrierBytes = 128;  // up to 16 mbarriers
+constexpr int kColumnBarrierBytes = 128;  // K1a: up to 16 "slot full" mbarriers
+constexpr int kRelayBarrierBytes = 256;   // K1b: 16 "slot full" + 16 "carry arrived"
 constexpr int kMaxDepth = 16;
+constexpr int kMaxWarps = 16;
 
 template <int N>
 __device__ __forceinline__ void load_row(float (&x)[N], const float* row) {
@@ -89,27 +96,49 @@ __device__ __forceinline__ void store_row(float* row, const float (&x)[N]) {
   }
 }
 
-// experiment.py:377-382
-__device__ __forceinline__ float clip_reward(float r, int mode) {
-  if (mode == VTR_REWARD_CLIP_ABS_ONE) return fminf(fmaxf(r, -1.0f), 1.0f);
-  if (mode == VTR_REWARD_CLIP_SOFT_ASYMMETRIC) {
-    const float squeezed = tanhf(r / 5.0f);
-    return (r < 0.0f ? 0.3f * squeezed : squeezed) * 5.0f;
-  }
-  return r;
-}
-
 __device__ __forceinline__ double warp_sum_fixed(double v) {
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
   return v;
 }
 
-// Everything one (t, column) step produces besides the gradient row.
-struct StepOut {
-  float vs, pg, log_rho, b_lp, t_lp;
-};
+// Fills ring slot `s` (shared address `dst`, mbarrier `bar`) with time step `t`
+// of the tile starting at column b0.  Called by all 32 lanes of one warp; the
+// barrier expects 33 arrivals: every lane's cp.async group + lane 0's arm.
+__device__ __forceinline__ void issue_step(const FusedArgs& a, int t, uint32_t dst, uint32_t bar,
+                                           int lane, int b0, int nb, int A, bool tma_in,
+                                           uint64_t policy) {
+  const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
+  const size_t row0 = (static_cast<size_t>(t) * a.B + b0) * A;
+  if (tma_in) {
+    if (lane == 0) {
+      ptx::mbar_arrive_expect_tx(bar, 2u * row_bytes);
+      ptx::bulk_g2s(dst, a.blog + row0, row_bytes, bar, policy);
+      ptx::bulk_g2s(dst + 32u * A * 4u, a.tlog + row0, row_bytes, bar, policy);
+    }
+  } else {
+    if (lane == 0) ptx::mbar_arrive(bar);
+    for (int i = lane; i < nb * A; i += 32) {
+      ptx::cp_async4(dst + 4u * i, a.blog + row0 + i);
+      ptx::cp_async4(dst + (32u * A + i) * 4u, a.tlog + row0 + i);
+    }
+  }
+  if (lane < nb) {
+    const size_t e = static_cast<size_t>(t) * a.B + b0 + lane;
+    const uint32_t sc = dst + (64u * A + lane) * 4u;
+    ptx::cp_async4(sc, a.actions + e);
+    if (a.discounts) ptx::cp_async4(sc + 128u, a.discounts + e);
+    ptx::cp_async4(sc + 256u, a.rewards + e);
+    ptx::cp_async4(sc + 384u, a.values + e);
+  }
+  ptx::cp_async_mbar_arrive_noinc(bar);
+}
 
+// ---------------------------------------------------------------------------
+// K1a: one warp per tile.  Used when an SM has to hold so many tiles (>= 7)
+// that shared memory allows only one warp's worth of ring per tile: the whole
+// ring (5 slots at A=18) then runs ahead of the single consumer.
+// ---------------------------------------------------------------------------
 template <int A_CT, bool GRADS>
 __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant__ FusedArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -121,16 +150,17 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
   const bool active = lane < nb;
   const int b = b0 + (active ? lane : 0);
   const int depth = a.depth;
-  const int stage_floats = a.stage_floats;
+  const int slot_floats = a.slot_floats;
 
-  float* ring = reinterpret_cast<float*>(smem_raw + kBarrierBytes);
-  float* outbuf = ring + static_cast<size_t>(depth) * stage_floats;  // 2 x [32*A], GRADS only
+  float* ring = reinterpret_cast<float*>(smem_raw + kColumnBarrierBytes);
+  float* outbuf = ring + static_cast<size_t>(depth) * slot_floats;  // 2 x [32*A], GRADS only
   const uint32_t bars = ptx::smem_u32(smem_raw);
   const uint32_t ring_u32 = ptx::smem_u32(ring);
   const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
   const int row_elems = nb * A;
   const bool tma_in = a.tma_in_ok && (row_bytes % 16u == 0);
   const bool tma_out = a.tma_out_ok && (row_bytes % 16u == 0);
+  const bool need_softmax = GRADS || a.partials != nullptr;
 
   if (lane == 0) {
     for (int s = 0; s < depth; ++s) ptx::mbar_init(bars + 8u * s, 33);
@@ -140,46 +170,18 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
   __syncwarp();
   const uint64_t policy = ptx::policy_evict_first();
 
-  // Fills stage `s` with time step `t` of this tile.
   auto issue = [&](int t, int s) {
-    const uint32_t bar = bars + 8u * s;
-    const uint32_t dst = ring_u32 + static_cast<uint32_t>(s) * stage_floats * 4u;
-    const size_t row0 = (static_cast<size_t>(t) * B + b0) * A;
-    if (tma_in) {
-      if (lane == 0) {
-        ptx::mbar_arrive_expect_tx(bar, 2u * row_bytes);
-        ptx::bulk_g2s(dst, a.blog + row0, row_bytes, bar, policy);
-        ptx::bulk_g2s(dst + 32u * A * 4u, a.tlog + row0, row_bytes, bar, policy);
-      }
-    } else {
-      if (lane == 0) ptx::mbar_arrive(bar);
-      for (int i = lane; i < row_elems; i += 32) {
-        ptx::cp_async4(dst + 4u * i, a.blog + row0 + i);
-        ptx::cp_async4(dst + (32u * A + i) * 4u, a.tlog + row0 + i);
-      }
-    }
-    if (active) {
-      const size_t e = static_cast<size_t>(t) * B + b;
-      const uint32_t sc = dst + (64u * A + lane) * 4u;
-      ptx::cp_async4(sc, a.actions + e);
-      if (a.discounts) ptx::cp_async4(sc + 128u, a.discounts + e);
-      ptx::cp_async4(sc + 256u, a.rewards + e);
-      ptx::cp_async4(sc + 384u, a.values + e);
-    }
-    ptx::cp_async_mbar_arrive_noinc(bar);
+    issue_step(a, t, ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u, bars + 8u * s, lane, b0,
+               nb, A, tma_in, policy);
   };
-
   const int prologue = min(depth, T);
   for (int k = 0; k < prologue; ++k) issue(T - 1 - k, k);
 
-  const bool no_clip_rho = a.flags & VTR_FLAG_NO_CLIP_RHO;
-  const bool no_clip_pg = a.flags & VTR_FLAG_NO_CLIP_PG_RHO;
-  const float ec = a.entropy_cost;
-
-  float acc = 0.0f;  // vs_{t+1} - V(x_{t+1}), initial value vtrace.py:256
-  float v_next = active ? a.bootstrap[b] : 0.0f;  // V(x_{t+1}), vtrace.py:243-244
-  float vs_next = v_next;                         // vs_{t+1},   vtrace.py:268-269
-  double pg_sum = 0.0, bl_sum = 0.0, ent_sum = 0.0;
+  math::Carry carry;
+  carry.acc = 0.0f;
+  carry.v_next = active ? a.bootstrap[b] : 0.0f;
+  carry.vs_next = carry.v_next;
+  math::LossSums sums = {0.0, 0.0, 0.0};
   uint8_t done_next = 0;
   if (a.done && active) done_next = a.done[static_cast<size_t>(T - 1) * B + b];
 
@@ -199,17 +201,17 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
     }
     ptx::mbar_wait(bars + 8u * s, parity);
 
-    const float* st = ring + static_cast<size_t>(s) * stage_floats;
-    const float* xb_row = st + lane * A;
-    const float* xt_row = st + 32 * A + lane * A;
-    const float* sc = st + 64 * A;
+    const float* slot = ring + static_cast<size_t>(s) * slot_floats;
+    const float* xb_row = slot + lane * A;
+    const float* xt_row = slot + 32 * A + lane * A;
+    const float* sc = slot + 64 * A;
     float* orow = outbuf + (it & 1) * 32 * A + lane * A;
 
     if (active) {
       int act = __float_as_int(sc[lane]);
       act = min(max(act, 0), A - 1);
-      float disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
-      const float rew = clip_reward(sc[64 + lane], a.reward_clip_mode);
+      const float disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
+      const float rew = math::clip_reward(sc[64 + lane], a.reward_clip_mode);
       const float val = sc[96 + lane];
 
       // ---- action log-probs of both policies (vtrace.py:143-146) ----
@@ -217,56 +219,23 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
       float d[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];
       if constexpr (A_CT > 0) {
         load_row(d, xt_row);
-        m_t = d[0];
-#pragma unroll
-        for (int i = 1; i < A_CT; ++i) m_t = fmaxf(m_t, d[i]);
-        float s0 = 0.0f, s1 = 0.0f;
-#pragma unroll
-        for (int i = 0; i < A_CT; ++i) {
-          d[i] -= m_t;
-          ex[i] = ptx::ex2(d[i] * kLog2e);
-          if (i & 1) s1 += ex[i]; else s0 += ex[i];
-        }
-        sum_t = s0 + s1;
+        sum_t = math::row_exp_terms(d, ex, m_t);
         float xb[A_CT];
         load_row(xb, xb_row);
-        m_b = xb[0];
-#pragma unroll
-        for (int i = 1; i < A_CT; ++i) m_b = fmaxf(m_b, xb[i]);
-        s0 = 0.0f, s1 = 0.0f;
-#pragma unroll
-        for (int i = 0; i < A_CT; ++i) {
-          const float v = ptx::ex2((xb[i] - m_b) * kLog2e);
-          if (i & 1) s1 += v; else s0 += v;
-        }
-        sum_b = s0 + s1;
+        sum_b = math::row_exp_sum(xb, m_b);
       } else {
-        m_t = xt_row[0], m_b = xb_row[0];
-        for (int i = 1; i < A; ++i) m_t = fmaxf(m_t, xt_row[i]), m_b = fmaxf(m_b, xb_row[i]);
-        sum_t = 0.0f, sum_b = 0.0f;
-        for (int i = 0; i < A; ++i) {
-          const float v = ptx::ex2((xt_row[i] - m_t) * kLog2e);
-          sum_t += v;
-          if (GRADS) orow[i] = v;
-          sum_b += ptx::ex2((xb_row[i] - m_b) * kLog2e);
-        }
+        sum_t = math::smem_row_exp_sum(xt_row, A, m_t);
+        sum_b = math::smem_row_exp_sum(xb_row, A, m_b);
       }
       const float ln_sum_t = logf(sum_t);
-      const float t_lp = (xt_row[act] - m_t) - ln_sum_t;
-      const float b_lp = (xb_row[act] - m_b) - logf(sum_b);
-      const float log_rho = t_lp - b_lp;  // vtrace.py:147
+      const float t_lp = math::action_log_prob(xt_row[act], m_t, ln_sum_t);
+      const float b_lp = math::action_log_prob(xb_row[act], m_b, logf(sum_b));
+      const float log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
 
       // ---- V-trace step (vtrace.py:235-276), walking t downwards ----
-      const float rho = expf(log_rho);
-      const float rho_hat = no_clip_rho ? rho : fminf(a.clip_rho, rho);
-      const float c = fminf(1.0f, rho);
-      const float rho_pg = no_clip_pg ? rho : fminf(a.clip_pg_rho, rho);
-      const float delta = rho_hat * (rew + disc * v_next - val);
-      acc = delta + disc * c * acc;
-      const float vs = acc + val;
-      const float pg = rho_pg * (rew + disc * vs_next - val);
-      v_next = val;
-      vs_next = vs;
+      const math::Weights w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
+      float vs, pg;
+      math::vtrace_step(w, rew, disc, val, carry, vs, pg);
 
       if (a.vs) a.vs[e] = vs;
       if (a.pg) a.pg[e] = pg;
@@ -275,49 +244,24 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
       if (a.t_lp) a.t_lp[e] = t_lp;
 
       // ---- losses (experiment.py:324-343) and their gradients ----
-      float entropy = 0.0f;
-      if (GRADS || a.partials) {
-        const float inv_sum = 1.0f / sum_t;
-        if constexpr (A_CT > 0) {
-          float h0 = 0.0f, h1 = 0.0f;
-#pragma unroll
-          for (int i = 0; i < A_CT; ++i) {
-            ex[i] *= inv_sum;      // p_i
-            d[i] -= ln_sum_t;      // log p_i
-            if (i & 1) h1 = fmaf(-ex[i], d[i], h1); else h0 = fmaf(-ex[i], d[i], h0);
-          }
-          entropy = h0 + h1;
-          if (GRADS) {
-            const float k = fmaf(ec, entropy, pg);
-#pragma unroll
-            for (int i = 0; i < A_CT; ++i) ex[i] *= fmaf(ec, d[i], k);
-            store_row(orow, ex);
-          }
-        } else {
-          for (int i = 0; i < A; ++i) {
-            const float p = (GRADS ? orow[i] : ptx::ex2((xt_row[i] - m_t) * kLog2e)) * inv_sum;
-            const float lp = (xt_row[i] - m_t) - ln_sum_t;
-            entropy = fmaf(-p, lp, entropy);
-          }
-          if (GRADS) {
-            const float k = fmaf(ec, entropy, pg);
-            for (int i = 0; i < A; ++i) {
-              const float p = orow[i] * inv_sum;
-              const float lp = (xt_row[i] - m_t) - ln_sum_t;
-              orow[i] = p * fmaf(ec, lp, k);
-            }
-          }
-        }
+      if (need_softmax) {
+        const float inv_sum = __fdiv_rn(1.0f, sum_t);
+        float entropy;
+        if constexpr (A_CT > 0) entropy = math::row_entropy(d, ex, inv_sum, ln_sum_t);
+        else entropy = math::smem_row_entropy(xt_row, A, m_t, inv_sum, ln_sum_t);
         if (GRADS) {
-          orow[act] -= pg;  // the -onehot(a) * pg_adv term
-          if (a.d_values) a.d_values[e] = a.baseline_cost * (val - vs);
+          // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
+          const float k = __fmaf_rn(a.entropy_cost, entropy, pg);
+          if constexpr (A_CT > 0) {
+            math::row_gradient(ex, d, a.entropy_cost, k);
+            store_row(orow, ex);
+          } else {
+            math::smem_row_gradient(orow, xt_row, A, m_t, inv_sum, ln_sum_t, a.entropy_cost, k);
+          }
+          orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
+          if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
         }
-        if (a.partials) {
-          pg_sum = fma(-static_cast<double>(t_lp), static_cast<double>(pg), pg_sum);
-          const double diff = static_cast<double>(vs) - static_cast<double>(val);
-          bl_sum = fma(0.5 * diff, diff, bl_sum);
-          ent_sum -= static_cast<double>(entropy);
-        }
+        if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
       }
     }
 
@@ -336,18 +280,237 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
         for (int i = lane; i < row_elems; i += 32) gdst[i] = src[i];
       }
     }
-    __syncwarp();  // every lane is done with stage s
+    __syncwarp();  // every lane is done with slot s
     if (it + depth < T) issue(t - depth, s);
     if (++s == depth) s = 0, parity ^= 1u;
   }
 
   if (a.partials) {
-    pg_sum = warp_sum_fixed(pg_sum);
-    bl_sum = warp_sum_fixed(bl_sum);
-    ent_sum = warp_sum_fixed(ent_sum);
+    const double pg_sum = warp_sum_fixed(sums.pg);
+    const double bl_sum = warp_sum_fixed(sums.baseline);
+    const double ent_sum = warp_sum_fixed(sums.entropy);
     if (lane == 0) {
       double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
       out[0] = pg_sum, out[1] = bl_sum, out[2] = ent_sum;
+    }
+  }
+  if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
+// K1b: several warps per tile, passing the recurrence along ("relay").  Warp w
+// owns the time steps it = w, w+W, ... (it counts from the end: t = T-1-it);
+// each does its whole step in its own registers and only the 3-float carry
+// (acc, V_{t+1}, vs_{t+1}) per lane travels from the owner of step t+1 to the
+// owner of step t, through shared memory and an mbarrier.  Everything that
+// does not depend on the carry (both softmaxes, log_rho, rho, the entropy:
+// most of the work) overlaps between warps, so a tile advances much faster
+// than one warp can; used whenever shared memory leaves room for it.
+//
+// Shared memory of one tile, in bytes from the start:
+//   [0,128)    `depth` mbarriers "slot full"      (TMA + cp.async completion)
+//   [128,256)  `warps` mbarriers "carry arrived"  (recurrence hand-off)
+//   ring       depth slots of slot_floats floats: one time step of the tile each
+//   staging    warps x 32*A floats: each warp's d_target_logits row  (GRADS only)
+//   carry      warps x 3 x 32 floats: (acc, V_{t+1}, vs_{t+1}) per lane
+//   sums       warps x 3 doubles: per-warp loss partials
+//
+// Launch bound 768 threads (never more than 512 are launched) caps the kernel
+// at 80 registers, so that 24 warps fit an SM's register file.
+// ---------------------------------------------------------------------------
+template <int A_CT, bool GRADS>
+__global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ FusedArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int A = A_CT > 0 ? A_CT : a.A;
+  const int T = a.T, B = a.B;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int W = blockDim.x >> 5;
+  const int b0 = blockIdx.x * kColumnsPerTile;
+  const int nb = min(kColumnsPerTile, B - b0);
+  const bool active = lane < nb;
+  const int b = b0 + (active ? lane : 0);
+  const int depth = a.depth;
+  const int slot_floats = a.slot_floats;
+
+  float* ring = reinterpret_cast<float*>(smem_raw + kRelayBarrierBytes);
+  float* staging = ring + static_cast<size_t>(depth) * slot_floats;
+  float* carry_buf = staging + (GRADS ? W * 32 * A : 0);
+  double* warp_sums = reinterpret_cast<double*>(carry_buf + W * 96);
+  const uint32_t full_bars = ptx::smem_u32(smem_raw);
+  const uint32_t carry_bars = full_bars + 128u;
+  const uint32_t ring_u32 = ptx::smem_u32(ring);
+  const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
+  const int row_elems = nb * A;
+  const bool tma_in = a.tma_in_ok && (row_bytes % 16u == 0);
+  const bool tma_out = a.tma_out_ok && (row_bytes % 16u == 0);
+  const bool need_softmax = GRADS || a.partials != nullptr;
+  float* orow_base = staging + warp * 32 * A;  // this warp's gradient row
+  float* orow = orow_base + lane * A;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < depth; ++s) ptx::mbar_init(full_bars + 8u * s, 33);
+    for (int w = 0; w < W; ++w) ptx::mbar_init(carry_bars + 8u * w, 32);
+    ptx::fence_mbar_init();
+    ptx::fence_proxy_async();
+  }
+  __syncthreads();
+  const uint64_t policy = ptx::policy_evict_first();
+
+  auto issue = [&](int t, int s) {
+    issue_step(a, t, ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u, full_bars + 8u * s, lane,
+               b0, nb, A, tma_in, policy);
+  };
+  // Step `it` lives in ring slot it % depth and is loaded by the warp that owns it.
+  for (int it = warp; it < min(depth, T); it += W) issue(T - 1 - it, it);
+
+  math::LossSums sums = {0.0, 0.0, 0.0};
+
+  for (int it = warp; it < T; it += W) {
+    const int t = T - 1 - it;
+    const size_t e = static_cast<size_t>(t) * B + b;
+    const int s = it % depth;
+    const uint8_t done_cur = (a.done && active) ? a.done[e] : 0;
+
+    ptx::mbar_wait(full_bars + 8u * s, (it / depth) & 1);
+    const float* slot = ring + static_cast<size_t>(s) * slot_floats;
+    const float* xb_row = slot + lane * A;
+    const float* xt_row = slot + 32 * A + lane * A;
+    const float* sc = slot + 64 * A;
+
+    // ---- phase A: everything that does not depend on step t+1 ----
+    int act = 0;
+    float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
+    float m_t = 0.0f, sum_t = 1.0f, m_b = 0.0f, sum_b = 1.0f;
+    float d[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];
+    if (active) {
+      act = __float_as_int(sc[lane]);
+      act = min(max(act, 0), A - 1);
+      disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
+      rew = sc[64 + lane];
+      val = sc[96 + lane];
+      xa_t = xt_row[act];
+      xa_b = xb_row[act];
+      if constexpr (A_CT > 0) {
+        // behaviour row first: it reduces to (max, sum) and frees its registers
+        float xb[A_CT];
+        load_row(xb, xb_row);
+        sum_b = math::row_exp_sum(xb, m_b);
+        load_row(d, xt_row);
+      }
+    }
+    if constexpr (A_CT > 0) {
+      // The rows are in registers: the slot can take step it+depth already.
+      __syncwarp();
+      if (it + depth < T) issue(t - depth, s);
+    }
+    float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f, ln_sum_t = 0.0f;
+    float entropy = 0.0f, inv_sum = 0.0f;
+    math::Weights w = {0.0f, 0.0f, 0.0f};
+    if (active) {
+      rew = math::clip_reward(rew, a.reward_clip_mode);
+      // action log-probs of both policies (vtrace.py:143-146)
+      if constexpr (A_CT > 0) {
+        sum_t = math::row_exp_terms(d, ex, m_t);
+      } else {
+        sum_t = math::smem_row_exp_sum(xt_row, A, m_t);
+        sum_b = math::smem_row_exp_sum(xb_row, A, m_b);
+      }
+      ln_sum_t = logf(sum_t);
+      t_lp = math::action_log_prob(xa_t, m_t, ln_sum_t);
+      b_lp = math::action_log_prob(xa_b, m_b, logf(sum_b));
+      log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
+      w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
+      if (need_softmax) {
+        inv_sum = __fdiv_rn(1.0f, sum_t);
+        if constexpr (A_CT > 0) entropy = math::row_entropy(d, ex, inv_sum, ln_sum_t);
+        else entropy = math::smem_row_entropy(xt_row, A, m_t, inv_sum, ln_sum_t);
+      }
+    }
+
+    // ---- phase B: the V-trace step (vtrace.py:243-276); needs step t+1 ----
+    math::Carry carry;
+    if (it == 0) {
+      carry.acc = 0.0f;
+      carry.v_next = active ? a.bootstrap[b] : 0.0f;
+      carry.vs_next = carry.v_next;
+    } else {
+      // n-th use of this warp's carry slot: steps warp, warp+W, ... (step 0 has none)
+      const int use = it / W - (warp == 0 ? 1 : 0);
+      ptx::mbar_wait(carry_bars + 8u * warp, use & 1);
+      const float* cb = carry_buf + warp * 96;
+      carry.acc = cb[lane], carry.v_next = cb[32 + lane], carry.vs_next = cb[64 + lane];
+    }
+    float vs, pg;
+    math::vtrace_step(w, rew, disc, val, carry, vs, pg);
+    if (it + 1 < T) {
+      const int nw = warp + 1 == W ? 0 : warp + 1;  // owner of step it+1
+      float* cb = carry_buf + nw * 96;
+      cb[lane] = carry.acc, cb[32 + lane] = carry.v_next, cb[64 + lane] = carry.vs_next;
+      ptx::mbar_arrive(carry_bars + 8u * nw);
+    }
+
+    // ---- phase C: outputs, gradient row, loss terms ----
+    if (GRADS) {
+      // this warp's previous bulk store must have read the staging row
+      if (tma_out && lane == 0) ptx::bulk_wait_read<0>();
+      __syncwarp();
+    }
+    if (active) {
+      if (a.vs) a.vs[e] = vs;
+      if (a.pg) a.pg[e] = pg;
+      if (a.log_rhos) a.log_rhos[e] = log_rho;
+      if (a.b_lp) a.b_lp[e] = b_lp;
+      if (a.t_lp) a.t_lp[e] = t_lp;
+      if (GRADS) {
+        // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
+        const float k = __fmaf_rn(a.entropy_cost, entropy, pg);
+        if constexpr (A_CT > 0) {
+          math::row_gradient(ex, d, a.entropy_cost, k);
+          store_row(orow, ex);
+        } else {
+          math::smem_row_gradient(orow, xt_row, A, m_t, inv_sum, ln_sum_t, a.entropy_cost, k);
+        }
+        orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
+        if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
+      }
+      if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
+    }
+    if (GRADS) {
+      float* gdst = a.d_logits + (static_cast<size_t>(t) * B + b0) * A;
+      if (tma_out) {
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          ptx::bulk_s2g(gdst, ptx::smem_u32(orow_base), row_bytes);
+          ptx::bulk_commit();
+        }
+      } else {
+        __syncwarp();
+        for (int i = lane; i < row_elems; i += 32) gdst[i] = orow_base[i];
+        __syncwarp();
+      }
+    }
+    if constexpr (A_CT == 0) {
+      // run-time A re-reads the rows from the slot: refill only now
+      __syncwarp();
+      if (it + depth < T) issue(t - depth, s);
+    }
+  }
+
+  if (a.partials) {
+    const double pg_sum = warp_sum_fixed(sums.pg);
+    const double bl_sum = warp_sum_fixed(sums.baseline);
+    const double ent_sum = warp_sum_fixed(sums.entropy);
+    if (lane == 0)
+      warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+      for (int w = 0; w < W; ++w)
+        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
+      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
+      out[0] = p0, out[1] = p1, out[2] = p2;
     }
   }
   if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
@@ -390,25 +553,44 @@ __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __rest
 static inline int column_tiles(int B) { return (B + kColumnsPerTile - 1) / kColumnsPerTile; }
 
 template <int A_CT, bool GRADS>
-static int launch_column(const FusedArgs& args, int tiles, size_t smem, cudaStream_t stream) {
-  auto kernel = fused_column_kernel<A_CT, GRADS>;
+static int launch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
+  auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
   VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       static_cast<int>(smem)));
-  kernel<<<tiles, 32, smem, stream>>>(args);
+  kernel<<<tiles, 32 * warps, smem, stream>>>(args);
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;
 }
 
 template <bool GRADS>
-static int dispatch_column(const FusedArgs& args, int tiles, size_t smem, cudaStream_t stream) {
+static int dispatch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
   switch (args.A) {
-    case 3: return launch_column<3, GRADS>(args, tiles, smem, stream);
-    case 4: return launch_column<4, GRADS>(args, tiles, smem, stream);
-    case 6: return launch_column<6, GRADS>(args, tiles, smem, stream);
-    case 9: return launch_column<9, GRADS>(args, tiles, smem, stream);
-    case 18: return launch_column<18, GRADS>(args, tiles, smem, stream);
-    default: return launch_column<0, GRADS>(args, tiles, smem, stream);
+    case 3: return launch_tiles<3, GRADS>(args, tiles, warps, smem, stream);
+    case 4: return launch_tiles<4, GRADS>(args, tiles, warps, smem, stream);
+    case 6: return launch_tiles<6, GRADS>(args, tiles, warps, smem, stream);
+    case 9: return launch_tiles<9, GRADS>(args, tiles, warps, smem, stream);
+    case 18: return launch_tiles<18, GRADS>(args, tiles, warps, smem, stream);
+    default: return launch_tiles<0, GRADS>(args, tiles, warps, smem, stream);
   }
+}
+
+// Tuning overrides for experiments (not part of the ABI):
+// VTR_COLUMN_WARPS in [1,16], VTR_COLUMN_DEPTH in [1,16].
+static int env_int(const char* name) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : 0;
+}
+
+static size_t slot_bytes_for(int A) {
+  return (2u * kColumnsPerTile * A + 4u * kColumnsPerTile) * sizeof(float);
+}
+
+// Shared memory of a tile with `warps` warps and `depth` ring slots.
+static size_t tile_smem_bytes(int A, int depth, int warps, bool grads) {
+  const size_t row = kColumnsPerTile * A * sizeof(float);
+  if (warps == 1) return kColumnBarrierBytes + depth * slot_bytes_for(A) + (grads ? 2 * row : 0);
+  const size_t per_warp = (grads ? row : 0) + 96 * sizeof(float) + 3 * sizeof(double);
+  return kRelayBarrierBytes + depth * slot_bytes_for(A) + warps * per_warp;
 }
 
 static int run_column_path(const vtr_fused_params* p, double* partials, cudaStream_t stream) {
@@ -439,29 +621,43 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   a.tma_in_ok = rows_aligned && aligned(a.blog, 16) && aligned(a.tlog, 16);
   a.tma_out_ok = rows_aligned && aligned(a.d_logits, 16);
 
-  // Ring depth: share the SM's shared memory between the tiles that will be
-  // co-resident on it, and keep as many time steps in flight as fit.
-  const size_t stage_bytes = (2u * kColumnsPerTile * p->A + 4u * kColumnsPerTile) * sizeof(float);
-  const size_t out_bytes = grads ? 2u * kColumnsPerTile * p->A * sizeof(float) : 0;
+  // Shared memory per tile = what the SM has, divided by the tiles that must be
+  // co-resident on it (everything runs in one wave up to 8 tiles per SM).
+  const size_t slot_bytes = slot_bytes_for(p->A);
   int resident = (tiles + dev.sm_count - 1) / dev.sm_count;
   resident = resident < 1 ? 1 : (resident > 8 ? 8 : resident);
   size_t budget = static_cast<size_t>(dev.smem_per_sm) / resident;
   budget = budget > 2048 ? budget - 1024 : budget;  // per-block reservation
   if (budget > static_cast<size_t>(dev.max_smem_optin)) budget = dev.max_smem_optin;
-  long depth = (static_cast<long>(budget) - static_cast<long>(out_bytes) - kBarrierBytes) /
-               static_cast<long>(stage_bytes);
+
+  // Warps per tile.  With 7+ tiles per SM the ring is worth more than extra
+  // warps (measured: T=100 B=32768 A=18 runs 142 us with one warp and 5 slots,
+  // 166 us with 3 warps and 4 slots); below that, aim at ~24 warps per SM while
+  // the ring still runs at least 2 slots ahead of the warps.
+  int warps = resident >= 7 ? 1 : 24 / resident;
+  if (const int forced = env_int("VTR_COLUMN_WARPS")) warps = forced;
+  if (warps > kMaxWarps) warps = kMaxWarps;
+  if (warps > p->T) warps = p->T;
+  if (warps < 1) warps = 1;
+  long depth = 0;
+  for (;; --warps) {
+    const size_t fixed = tile_smem_bytes(p->A, 0, warps, grads);
+    depth = budget > fixed ? static_cast<long>((budget - fixed) / slot_bytes) : 0;
+    if (warps == 1 || depth >= warps + 2) break;
+  }
+  if (const int forced = env_int("VTR_COLUMN_DEPTH")) depth = forced;
   if (depth > kMaxDepth) depth = kMaxDepth;
   if (depth > p->T) depth = p->T;
   if (depth < 2) depth = p->T < 2 ? 1 : 2;
-  const size_t smem = kBarrierBytes + depth * stage_bytes + out_bytes;
+  const size_t smem = tile_smem_bytes(p->A, static_cast<int>(depth), warps, grads);
   if (smem > static_cast<size_t>(dev.max_smem_optin))
     return fail(VTR_ERR_UNSUPPORTED, "A=%d needs %zu bytes of shared memory, device allows %d",
                 p->A, smem, dev.max_smem_optin);
   a.depth = static_cast<int>(depth);
-  a.stage_floats = static_cast<int>(stage_bytes / sizeof(float));
+  a.slot_floats = static_cast<int>(slot_bytes / sizeof(float));
 
-  return grads ? dispatch_column<true>(a, tiles, smem, stream)
-               : dispatch_column<false>(a, tiles, smem, stream);
+  return grads ? dispatch_tiles<true>(a, tiles, warps, smem, stream)
+               : dispatch_tiles<false>(a, tiles, warps, smem, stream);
 }
 
 }  // namespace vtr
