@@ -44,6 +44,7 @@ def main():
   ap.add_argument('--paths', default='auto')
   ap.add_argument('--only', default='')
   ap.add_argument('--extra', default='', help='extra shapes: TxBxA,TxBxA')
+  ap.add_argument('--long', action='store_true', help='20x more warm iterations')
   args = ap.parse_args()
   device = torch.device('cuda', 0)
   torch.cuda.set_device(0)
@@ -80,6 +81,10 @@ def main():
           torch.cuda.synchronize()
           cold.append(s.elapsed_time(e) * 1e3)
         iters = 200 if T * B < 4e6 else 50
+        if args.long:
+          iters *= 20
+        sampler = bench.ClockSampler(bench.physical_gpu_index(0))
+        sampler.start()
         s = torch.cuda.Event(enable_timing=True)
         e = torch.cuda.Event(enable_timing=True)
         s.record()
@@ -87,6 +92,8 @@ def main():
           call()
         e.record()
         torch.cuda.synchronize()
+        sampler.stop()
+        clocks = sampler.summary()
         warm_us = s.elapsed_time(e) * 1e3 / iters
         alg = bench.algorithmic_bytes(T, B, A)
         cold_us = statistics.median(cold)
@@ -96,13 +103,14 @@ def main():
             'timesteps_per_s_warm': T * B / (warm_us * 1e-6),
             'GBps_cold': alg / cold_us / 1e3, 'GBps_warm': alg / warm_us / 1e3,
             'frac_peak_warm': alg / warm_us / 1e3 / peak,
-            'roofline_us': alg / peak / 1e3,
+            'roofline_us': alg / peak / 1e3, 'clocks': clocks,
         }
         f.write(json.dumps(rec) + '\n')
         f.flush()
         print('%-24s path=%-6s cold %8.1f us  warm %8.1f us  %7.0f GB/s (%.2f of peak) '
-              'roofline %.1f us' % (name, path, cold_us, warm_us, rec['GBps_warm'],
-                                    rec['frac_peak_warm'], rec['roofline_us']))
+              'roofline %.1f us  sm %s MHz %s' % (name, path, cold_us, warm_us, rec['GBps_warm'],
+                                    rec['frac_peak_warm'], rec['roofline_us'],
+                                    clocks['sm_mhz'], ','.join(clocks['reasons'])))
       del inp
       torch.cuda.empty_cache()
 

@@ -58,8 +58,8 @@ extern "C" {
 
 /* kernel selection for the fused entry point (0 = library decides) */
 #define VTR_PATH_AUTO 0
-#define VTR_PATH_COLUMN 1 /* thread-per-column, wide B                       */
-#define VTR_PATH_SCAN 2   /* T-parallel affine scan, small B                 */
+#define VTR_PATH_COLUMN 1  /* 32-column tiles, one ring per tile (any alignment) */
+#define VTR_PATH_SM_TILE 2 /* one wide tile per SM, shared ring (16-B aligned)  */
 
 int vtr_version(void);
 

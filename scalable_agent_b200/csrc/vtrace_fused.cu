@@ -207,29 +207,43 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
     const float* sc = slot + 64 * A;
     float* orow = outbuf + (it & 1) * 32 * A + lane * A;
 
+    // ---- operands and rows out of the slot ----
+    int act = 0;
+    float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
+    math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
+    float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
     if (active) {
-      int act = __float_as_int(sc[lane]);
+      act = __float_as_int(sc[lane]);
       act = min(max(act, 0), A - 1);
-      const float disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
-      const float rew = math::clip_reward(sc[64 + lane], a.reward_clip_mode);
-      const float val = sc[96 + lane];
-
-      // ---- action log-probs of both policies (vtrace.py:143-146) ----
-      float m_t, sum_t, m_b, sum_b;
-      float d[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];
+      disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
+      rew = sc[64 + lane];
+      val = sc[96 + lane];
+      xa_t = xt_row[act];
+      xa_b = xb_row[act];
       if constexpr (A_CT > 0) {
-        load_row(d, xt_row);
-        sum_t = math::row_exp_terms(d, ex, m_t);
         float xb[A_CT];
         load_row(xb, xb_row);
-        sum_b = math::row_exp_sum(xb, m_b);
-      } else {
-        sum_t = math::smem_row_exp_sum(xt_row, A, m_t);
-        sum_b = math::smem_row_exp_sum(xb_row, A, m_b);
+        sb = math::row_stats(xb);
+        load_row(x, xt_row);
       }
-      const float ln_sum_t = logf(sum_t);
-      const float t_lp = math::action_log_prob(xt_row[act], m_t, ln_sum_t);
-      const float b_lp = math::action_log_prob(xb_row[act], m_b, logf(sum_b));
+    }
+    if constexpr (A_CT > 0) {
+      // The rows are in registers: the slot can take step it+depth already.
+      __syncwarp();
+      if (it + depth < T) issue(t - depth, s);
+    }
+
+    if (active) {
+      rew = math::clip_reward(rew, a.reward_clip_mode);
+      // ---- action log-probs of both policies (vtrace.py:143-146) ----
+      if constexpr (A_CT > 0) {
+        st = math::row_stats(x, ex);
+      } else {
+        st = math::smem_row_stats(xt_row, A);
+        sb = math::smem_row_stats(xb_row, A);
+      }
+      const float t_lp = math::action_log_prob(xa_t, st);
+      const float b_lp = math::action_log_prob(xa_b, sb);
       const float log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
 
       // ---- V-trace step (vtrace.py:235-276), walking t downwards ----
@@ -245,18 +259,19 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
 
       // ---- losses (experiment.py:324-343) and their gradients ----
       if (need_softmax) {
-        const float inv_sum = __fdiv_rn(1.0f, sum_t);
+        const float inv_sum = __frcp_rn(st.sum);
         float entropy;
-        if constexpr (A_CT > 0) entropy = math::row_entropy(d, ex, inv_sum, ln_sum_t);
-        else entropy = math::smem_row_entropy(xt_row, A, m_t, inv_sum, ln_sum_t);
+        if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
+        else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
         if (GRADS) {
           // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
-          const float k = __fmaf_rn(a.entropy_cost, entropy, pg);
+          const float ka = __fmul_rn(a.entropy_cost, inv_sum);
+          const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
           if constexpr (A_CT > 0) {
-            math::row_gradient(ex, d, a.entropy_cost, k);
+            math::row_gradient(ex, x, ka, kb);
             store_row(orow, ex);
           } else {
-            math::smem_row_gradient(orow, xt_row, A, m_t, inv_sum, ln_sum_t, a.entropy_cost, k);
+            math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
           }
           orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
           if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
@@ -280,8 +295,11 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
         for (int i = lane; i < row_elems; i += 32) gdst[i] = src[i];
       }
     }
-    __syncwarp();  // every lane is done with slot s
-    if (it + depth < T) issue(t - depth, s);
+    if constexpr (A_CT == 0) {
+      // run-time A re-reads the rows from the slot: refill only now
+      __syncwarp();
+      if (it + depth < T) issue(t - depth, s);
+    }
     if (++s == depth) s = 0, parity ^= 1u;
   }
 
@@ -381,8 +399,8 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
     // ---- phase A: everything that does not depend on step t+1 ----
     int act = 0;
     float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
-    float m_t = 0.0f, sum_t = 1.0f, m_b = 0.0f, sum_b = 1.0f;
-    float d[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];
+    math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
+    float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
     if (active) {
       act = __float_as_int(sc[lane]);
       act = min(max(act, 0), A - 1);
@@ -392,11 +410,11 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       xa_t = xt_row[act];
       xa_b = xb_row[act];
       if constexpr (A_CT > 0) {
-        // behaviour row first: it reduces to (max, sum) and frees its registers
+        // behaviour row first: it reduces to its statistics and frees its registers
         float xb[A_CT];
         load_row(xb, xb_row);
-        sum_b = math::row_exp_sum(xb, m_b);
-        load_row(d, xt_row);
+        sb = math::row_stats(xb);
+        load_row(x, xt_row);
       }
     }
     if constexpr (A_CT > 0) {
@@ -404,27 +422,26 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       __syncwarp();
       if (it + depth < T) issue(t - depth, s);
     }
-    float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f, ln_sum_t = 0.0f;
+    float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
     float entropy = 0.0f, inv_sum = 0.0f;
     math::Weights w = {0.0f, 0.0f, 0.0f};
     if (active) {
       rew = math::clip_reward(rew, a.reward_clip_mode);
       // action log-probs of both policies (vtrace.py:143-146)
       if constexpr (A_CT > 0) {
-        sum_t = math::row_exp_terms(d, ex, m_t);
+        st = math::row_stats(x, ex);
       } else {
-        sum_t = math::smem_row_exp_sum(xt_row, A, m_t);
-        sum_b = math::smem_row_exp_sum(xb_row, A, m_b);
+        st = math::smem_row_stats(xt_row, A);
+        sb = math::smem_row_stats(xb_row, A);
       }
-      ln_sum_t = logf(sum_t);
-      t_lp = math::action_log_prob(xa_t, m_t, ln_sum_t);
-      b_lp = math::action_log_prob(xa_b, m_b, logf(sum_b));
+      t_lp = math::action_log_prob(xa_t, st);
+      b_lp = math::action_log_prob(xa_b, sb);
       log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
       w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
       if (need_softmax) {
-        inv_sum = __fdiv_rn(1.0f, sum_t);
-        if constexpr (A_CT > 0) entropy = math::row_entropy(d, ex, inv_sum, ln_sum_t);
-        else entropy = math::smem_row_entropy(xt_row, A, m_t, inv_sum, ln_sum_t);
+        inv_sum = __frcp_rn(st.sum);
+        if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
+        else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
       }
     }
 
@@ -464,12 +481,13 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       if (a.t_lp) a.t_lp[e] = t_lp;
       if (GRADS) {
         // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
-        const float k = __fmaf_rn(a.entropy_cost, entropy, pg);
+        const float ka = __fmul_rn(a.entropy_cost, inv_sum);
+        const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
         if constexpr (A_CT > 0) {
-          math::row_gradient(ex, d, a.entropy_cost, k);
+          math::row_gradient(ex, x, ka, kb);
           store_row(orow, ex);
         } else {
-          math::smem_row_gradient(orow, xt_row, A, m_t, inv_sum, ln_sum_t, a.entropy_cost, k);
+          math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
         }
         orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
         if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
@@ -514,6 +532,275 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
     }
   }
   if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
+// K1c: one persistent tile per SM ("SM tile").  The batch is split into
+// G (a multiple of the SM count) contiguous column ranges of equal width, up
+// to 256 columns each, so every SM streams the same number of bytes.  All
+// column groups of a tile share ONE ring: a producer warp fills slot after slot
+// with six TMA bulk copies per time step (two logits rows of ncols*A floats,
+// four operand rows of ncols floats: runs of up to 18 KB, which keeps DRAM
+// pages open), consumer warps wait on the slot's "full" mbarrier, pull their
+// rows into registers and hand the slot back through its "empty" mbarrier
+// straight away, long before their arithmetic is done.  Consumer warp
+// (g, r) owns columns [32g, 32g+32) of the tile and the time steps
+// it = r, r+R, ...; the R warps of a column group relay the recurrence carry
+// as in K1b (R = 1: the carry stays in registers).  Needs 16-byte aligned
+// rows: B % 4 == 0 and 16-byte aligned base pointers; anything else goes to
+// K1a/K1b.
+//
+// Shared memory of one tile, in bytes from the start:
+//   [0,128)    depth mbarriers "slot full"   (count 1 + tx bytes)
+//   [128,256)  depth mbarriers "slot empty"  (count = column groups)
+//   [256,384)  groups*relay mbarriers "carry arrived" (count 32)
+//   ring       depth slots: blog[cols*A] tlog[cols*A] actions[cols] discounts[cols]
+//              rewards[cols] values[cols], cols = 32*groups
+//   staging    per consumer warp, staging_bufs x 32*A floats   (GRADS only)
+//   carry      per consumer warp 3 x 32 floats
+//   sums       per consumer warp 3 doubles
+// ---------------------------------------------------------------------------
+constexpr int kSmBarrierBytes = 384;
+constexpr int kSmMaxConsumerWarps = 16;
+
+struct SmTileArgs {
+  FusedArgs f;
+  int groups;        // column groups (warps side by side) per tile
+  int relay;         // warps per column group, owning interleaved time steps
+  int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
+};
+
+template <int A_CT, bool GRADS>
+__global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
+    fused_sm_tile_kernel(const __grid_constant__ SmTileArgs args) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const FusedArgs& a = args.f;
+  const int A = A_CT > 0 ? A_CT : a.A;
+  const int T = a.T, B = a.B;
+  const int NG = args.groups, R = args.relay, depth = a.depth;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int consumers = NG * R;
+  const int cols = 32 * NG;  // slot stride in columns
+
+  // this tile's column range: B/4 granules of 4 columns dealt evenly to the grid
+  const int total_gran = B >> 2, G = gridDim.x, c = blockIdx.x;
+  const int base = total_gran / G, rem = total_gran % G;
+  const int col0 = (c * base + min(c, rem)) * 4;
+  const int ncols = (base + (c < rem ? 1 : 0)) * 4;
+
+  const int slot_floats = cols * (2 * A + 4);
+  float* ring = reinterpret_cast<float*>(smem_raw + kSmBarrierBytes);
+  float* staging = ring + static_cast<size_t>(depth) * slot_floats;
+  float* carry_buf = staging + (GRADS ? consumers * args.staging_bufs * 32 * A : 0);
+  double* warp_sums = reinterpret_cast<double*>(carry_buf + consumers * 96);
+  const uint32_t full_bars = ptx::smem_u32(smem_raw);
+  const uint32_t empty_bars = full_bars + 128u;
+  const uint32_t carry_bars = full_bars + 256u;
+  const uint32_t ring_u32 = ptx::smem_u32(ring);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < depth; ++s) {
+      ptx::mbar_init(full_bars + 8u * s, 1);
+      ptx::mbar_init(empty_bars + 8u * s, NG);
+    }
+    for (int w = 0; w < consumers; ++w) ptx::mbar_init(carry_bars + 8u * w, 32);
+    ptx::fence_mbar_init();
+    ptx::fence_proxy_async();
+  }
+  __syncthreads();
+
+  if (warp == consumers) {
+    // ---- producer: one lane keeps the ring full ----
+    if (lane == 0) {
+      const uint64_t policy = ptx::policy_evict_first();
+      const uint32_t logit_bytes = static_cast<uint32_t>(ncols) * A * 4u;
+      const uint32_t oper_bytes = static_cast<uint32_t>(ncols) * 4u;
+      const uint32_t tx = 2u * logit_bytes + (a.discounts ? 4u : 3u) * oper_bytes;
+      for (int it = 0; it < T; ++it) {
+        const int s = it % depth, n = it / depth;
+        if (n > 0) ptx::mbar_wait(empty_bars + 8u * s, (n - 1) & 1);
+        const int t = T - 1 - it;
+        const uint32_t bar = full_bars + 8u * s;
+        const uint32_t dst = ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u;
+        const size_t e0 = static_cast<size_t>(t) * B + col0;
+        ptx::mbar_arrive_expect_tx(bar, tx);
+        ptx::bulk_g2s(dst, a.blog + e0 * A, logit_bytes, bar, policy);
+        ptx::bulk_g2s(dst + cols * A * 4u, a.tlog + e0 * A, logit_bytes, bar, policy);
+        const uint32_t op = dst + 2u * cols * A * 4u;
+        ptx::bulk_g2s(op, a.actions + e0, oper_bytes, bar, policy);
+        if (a.discounts) ptx::bulk_g2s(op + cols * 4u, a.discounts + e0, oper_bytes, bar, policy);
+        ptx::bulk_g2s(op + 2u * cols * 4u, a.rewards + e0, oper_bytes, bar, policy);
+        ptx::bulk_g2s(op + 3u * cols * 4u, a.values + e0, oper_bytes, bar, policy);
+      }
+    }
+  } else {
+    // ---- consumers ----
+    const int g = warp % NG, r = warp / NG;
+    const int j = 32 * g + lane;  // column within the tile
+    const bool active = j < ncols;
+    const int b = col0 + (active ? j : 0);
+    const int nb = max(0, min(32, ncols - 32 * g));  // columns of this group
+    const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
+    const bool need_softmax = GRADS || a.partials != nullptr;
+    float* stage_base = staging + static_cast<size_t>(warp) * args.staging_bufs * 32 * A;
+    int stage_sel = 0;
+
+    math::Carry carry;  // R == 1: lives here across steps
+    carry.acc = 0.0f;
+    carry.v_next = active ? a.bootstrap[b] : 0.0f;
+    carry.vs_next = carry.v_next;
+    math::LossSums sums = {0.0, 0.0, 0.0};
+    // `done` flags (experiment.py:384) come straight from global memory, one
+    // owned step ahead.
+    uint8_t done_next = 0;
+    if (a.done && active && r < T) done_next = a.done[static_cast<size_t>(T - 1 - r) * B + b];
+
+    for (int it = r; it < T; it += R) {
+      const int t = T - 1 - it;
+      const size_t e = static_cast<size_t>(t) * B + b;
+      const int s = it % depth;
+      const uint8_t done_cur = done_next;
+      if (a.done && active && it + R < T) done_next = a.done[e - static_cast<size_t>(R) * B];
+
+      ptx::mbar_wait(full_bars + 8u * s, (it / depth) & 1);
+      const float* slot = ring + static_cast<size_t>(s) * slot_floats;
+      const float* xb_row = slot + j * A;
+      const float* xt_row = slot + cols * A + j * A;
+      const float* op = slot + 2 * cols * A;
+
+      // ---- phase A: everything that does not depend on step t+1 ----
+      int act = 0;
+      float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
+      math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
+      float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
+      if (active) {
+        act = __float_as_int(op[j]);
+        act = min(max(act, 0), A - 1);
+        disc = a.done ? (done_cur ? 0.0f : a.discounting) : op[cols + j];
+        rew = op[2 * cols + j];
+        val = op[3 * cols + j];
+        xa_t = xt_row[act];
+        xa_b = xb_row[act];
+        if constexpr (A_CT > 0) {
+          float xb[A_CT];
+          load_row(xb, xb_row);
+          sb = math::row_stats(xb);
+          load_row(x, xt_row);
+        }
+      }
+      if constexpr (A_CT > 0) {
+        // Rows are in registers: give the slot back to the producer.
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(empty_bars + 8u * s);
+      }
+      float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f, entropy = 0.0f, inv_sum = 0.0f;
+      math::Weights w = {0.0f, 0.0f, 0.0f};
+      if (active) {
+        rew = math::clip_reward(rew, a.reward_clip_mode);
+        if constexpr (A_CT > 0) {
+          st = math::row_stats(x, ex);
+        } else {
+          st = math::smem_row_stats(xt_row, A);
+          sb = math::smem_row_stats(xb_row, A);
+        }
+        t_lp = math::action_log_prob(xa_t, st);
+        b_lp = math::action_log_prob(xa_b, sb);
+        log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
+        w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
+        if (need_softmax) {
+          inv_sum = __frcp_rn(st.sum);
+          if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
+          else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
+        }
+      }
+
+      // ---- phase B: the V-trace step (vtrace.py:243-276); needs step t+1 ----
+      if (R > 1 && it > 0) {
+        // n-th use of this warp's carry slot (step 0 of the tile has none)
+        const int use = it / R - (r == 0 ? 1 : 0);
+        ptx::mbar_wait(carry_bars + 8u * warp, use & 1);
+        const float* cb = carry_buf + warp * 96;
+        carry.acc = cb[lane], carry.v_next = cb[32 + lane], carry.vs_next = cb[64 + lane];
+      }
+      float vs, pg;
+      math::vtrace_step(w, rew, disc, val, carry, vs, pg);
+      if (R > 1 && it + 1 < T) {
+        const int nw = (r + 1 == R ? 0 : r + 1) * NG + g;  // owner of step it+1
+        float* cb = carry_buf + nw * 96;
+        cb[lane] = carry.acc, cb[32 + lane] = carry.v_next, cb[64 + lane] = carry.vs_next;
+        ptx::mbar_arrive(carry_bars + 8u * nw);
+      }
+
+      // ---- phase C: outputs, gradient row, loss terms ----
+      float* orow_base = stage_base + stage_sel * 32 * A;
+      float* orow = orow_base + lane * A;
+      if (GRADS) {
+        // the bulk store that last read this staging row must be done with it
+        if (lane == 0) {
+          if (args.staging_bufs == 2) ptx::bulk_wait_read<1>();
+          else ptx::bulk_wait_read<0>();
+        }
+        __syncwarp();
+      }
+      if (active) {
+        if (a.vs) a.vs[e] = vs;
+        if (a.pg) a.pg[e] = pg;
+        if (a.log_rhos) a.log_rhos[e] = log_rho;
+        if (a.b_lp) a.b_lp[e] = b_lp;
+        if (a.t_lp) a.t_lp[e] = t_lp;
+        if (GRADS) {
+          // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
+          const float ka = __fmul_rn(a.entropy_cost, inv_sum);
+          const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
+          if constexpr (A_CT > 0) {
+            math::row_gradient(ex, x, ka, kb);
+            store_row(orow, ex);
+          } else {
+            math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
+          }
+          orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
+          if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
+        }
+        if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
+      }
+      if (GRADS) {
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0 && nb > 0) {
+          ptx::bulk_s2g(a.d_logits + (static_cast<size_t>(t) * B + col0 + 32 * g) * A,
+                        ptx::smem_u32(orow_base), row_bytes);
+          ptx::bulk_commit();
+        }
+        if (args.staging_bufs == 2) stage_sel ^= 1;
+      }
+      if constexpr (A_CT == 0) {
+        // run-time A re-reads the rows from the slot: release it only now
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(empty_bars + 8u * s);
+      }
+    }
+
+    if (a.partials) {
+      const double pg_sum = warp_sum_fixed(sums.pg);
+      const double bl_sum = warp_sum_fixed(sums.baseline);
+      const double ent_sum = warp_sum_fixed(sums.entropy);
+      if (lane == 0)
+        warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
+    }
+    if (GRADS && lane == 0) ptx::bulk_wait<0>();
+  }
+
+  if (a.partials) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+      for (int w = 0; w < consumers; ++w)
+        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
+      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
+      out[0] = p0, out[1] = p1, out[2] = p2;
+    }
+  }
 }
 
 // K3: second stage of the loss reduction.  One block, fixed summation order.
@@ -593,13 +880,7 @@ static size_t tile_smem_bytes(int A, int depth, int warps, bool grads) {
   return kRelayBarrierBytes + depth * slot_bytes_for(A) + warps * per_warp;
 }
 
-static int run_column_path(const vtr_fused_params* p, double* partials, cudaStream_t stream) {
-  DeviceInfo dev;
-  if (int rc = device_info(&dev)) return rc;
-  const int tiles = column_tiles(p->B);
-  const bool grads = p->d_target_logits != nullptr;
-
-  FusedArgs a;
+static void fill_args(FusedArgs& a, const vtr_fused_params* p, double* partials) {
   a.T = p->T, a.B = p->B, a.A = p->A;
   a.flags = p->flags;
   a.reward_clip_mode = p->reward_clip_mode;
@@ -614,6 +895,125 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   a.b_lp = p->behaviour_action_log_probs, a.t_lp = p->target_action_log_probs;
   a.d_logits = p->d_target_logits, a.d_values = p->d_values;
   a.partials = partials;
+  a.depth = 0, a.slot_floats = 0, a.tma_in_ok = 0, a.tma_out_ok = 0;
+}
+
+// K1c needs every row it bulk-copies to start and end on 16 bytes.
+static bool sm_tile_eligible(const vtr_fused_params* p) {
+  if (p->B % 4 != 0) return false;
+  const void* ptrs[] = {p->behaviour_policy_logits, p->target_policy_logits, p->actions, p->rewards,
+                        p->values, p->done ? nullptr : p->discounts, p->d_target_logits};
+  for (const void* q : ptrs)
+    if (!aligned(q, 16)) return false;
+  return true;
+}
+
+// VTR_PATH_AUTO: K1c from two 32-column groups per SM upwards (measured on
+// B200 at T=100, A=18: B=16384 81 us vs 90 us for K1b, B=49152 220 us vs
+// 278 us); below that its single producer lane is the bottleneck and K1b,
+// where every warp loads its own steps, is faster (B=4096: 26 us vs 45 us).
+static bool sm_tile_preferred(const vtr_fused_params* p) {
+  DeviceInfo dev;
+  if (device_info(&dev) != VTR_OK) return false;
+  return sm_tile_eligible(p) && p->B >= 64 * dev.sm_count;
+}
+
+template <int A_CT, bool GRADS>
+static int launch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStream_t stream) {
+  auto kernel = fused_sm_tile_kernel<A_CT, GRADS>;
+  VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));
+  kernel<<<grid, 32 * (args.groups * args.relay + 1), smem, stream>>>(args);
+  VTR_CUDA_CHECK(cudaGetLastError());
+  return VTR_OK;
+}
+
+template <bool GRADS>
+static int dispatch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStream_t stream) {
+  switch (args.f.A) {
+    case 3: return launch_sm_tile<3, GRADS>(args, grid, smem, stream);
+    case 4: return launch_sm_tile<4, GRADS>(args, grid, smem, stream);
+    case 6: return launch_sm_tile<6, GRADS>(args, grid, smem, stream);
+    case 9: return launch_sm_tile<9, GRADS>(args, grid, smem, stream);
+    case 18: return launch_sm_tile<18, GRADS>(args, grid, smem, stream);
+    default: return launch_sm_tile<0, GRADS>(args, grid, smem, stream);
+  }
+}
+
+// K1c launch: `*num_partials` = tiles written.  Returns VTR_ERR_UNSUPPORTED
+// without launching if the shape does not fit this kernel's shared memory.
+static int run_sm_tile_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
+                            int* num_partials) {
+  DeviceInfo dev;
+  if (int rc = device_info(&dev)) return rc;
+  const bool grads = p->d_target_logits != nullptr;
+  const int sm = dev.sm_count;
+  const int total_gran = p->B / 4;
+
+  // Grid: equal column ranges; a multiple of the SM count once the batch is
+  // wide enough to give every SM at least one 32-column group.
+  int waves = 1, grid;
+  if (p->B < 32 * sm) {
+    grid = (p->B + 31) / 32;
+  } else {
+    waves = (p->B + sm * 256 - 1) / (sm * 256);
+    grid = sm * waves;
+  }
+  const int ncols_max = ((total_gran + grid - 1) / grid) * 4;
+  SmTileArgs args;
+  fill_args(args.f, p, partials);
+  args.groups = (ncols_max + 31) / 32;
+
+  // Consumer warps: ~16 per SM.  Two tiles share an SM when the batch needs
+  // two or more waves, so that the waves overlap instead of queueing.
+  const int co_resident = waves >= 2 ? 2 : 1;
+  int relay = kSmMaxConsumerWarps / co_resident / args.groups;
+  if (const int forced = env_int("VTR_SM_RELAY")) relay = forced;
+  if (relay > p->T) relay = p->T;
+  if (relay * args.groups > kSmMaxConsumerWarps) relay = kSmMaxConsumerWarps / args.groups;
+  if (relay < 1) relay = 1;
+
+  size_t budget = static_cast<size_t>(dev.smem_per_sm) / co_resident;
+  budget = budget > 2048 ? budget - 1024 : budget;
+  if (budget > static_cast<size_t>(dev.max_smem_optin)) budget = dev.max_smem_optin;
+  const size_t row = 32 * static_cast<size_t>(p->A) * sizeof(float);
+  const size_t slot_bytes = 32u * args.groups * (2u * p->A + 4u) * sizeof(float);
+  size_t fixed = 0;
+  long depth = 0;
+  for (;; --relay) {
+    args.relay = relay;
+    args.staging_bufs = relay == 1 ? 2 : 1;
+    fixed = kSmBarrierBytes + args.groups * relay *
+                                  ((grads ? args.staging_bufs * row : 0) + 96 * sizeof(float) +
+                                   3 * sizeof(double));
+    depth = budget > fixed ? static_cast<long>((budget - fixed) / slot_bytes) : 0;
+    if (const int forced = env_int("VTR_COLUMN_DEPTH")) depth = forced;
+    if (depth > kMaxDepth) depth = kMaxDepth;
+    if (depth > p->T) depth = p->T;
+    // A warp waits for use n of a slot by parity, which only means something
+    // once use n-1 has completed.  The relay order guarantees that for steps
+    // more than `relay` back, so a reused slot must be further back than that.
+    if (relay == 1 || depth >= p->T || relay < depth) break;
+  }
+  if (depth < 2 && p->T >= 2) return fail(VTR_ERR_UNSUPPORTED, "sm-tile kernel: ring does not fit");
+  if (depth < 1) depth = 1;
+  args.f.depth = static_cast<int>(depth);
+  const size_t smem = fixed + depth * slot_bytes;
+  *num_partials = grid;
+  return grads ? dispatch_sm_tile<true>(args, grid, smem, stream)
+               : dispatch_sm_tile<false>(args, grid, smem, stream);
+}
+
+static int run_column_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
+                           int* num_partials) {
+  DeviceInfo dev;
+  if (int rc = device_info(&dev)) return rc;
+  const int tiles = column_tiles(p->B);
+  const bool grads = p->d_target_logits != nullptr;
+  *num_partials = tiles;
+
+  FusedArgs a;
+  fill_args(a, p, partials);
 
   // A row of the tile for step t starts at element (t*B + 32*tile)*A; TMA bulk
   // copies need 16-byte alignment of every such address.
@@ -649,6 +1049,10 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   if (depth > kMaxDepth) depth = kMaxDepth;
   if (depth > p->T) depth = p->T;
   if (depth < 2) depth = p->T < 2 ? 1 : 2;
+  // Waiting on a slot by parity needs the slot's previous use to be complete;
+  // the relay order guarantees that only for steps more than `warps` back.
+  if (depth < p->T && warps >= depth) warps = static_cast<int>(depth) - 1;
+  if (warps < 1) warps = 1;
   const size_t smem = tile_smem_bytes(p->A, static_cast<int>(depth), warps, grads);
   if (smem > static_cast<size_t>(dev.max_smem_optin))
     return fail(VTR_ERR_UNSUPPORTED, "A=%d needs %zu bytes of shared memory, device allows %d",
@@ -693,7 +1097,7 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     return fail(VTR_ERR_INVALID_ARGUMENT, "one of discounts / done must be given");
   if (p->reward_clip_mode < VTR_REWARD_CLIP_NONE || p->reward_clip_mode > VTR_REWARD_CLIP_SOFT_ASYMMETRIC)
     return fail(VTR_ERR_UNSUPPORTED, "unknown reward_clip_mode %d", p->reward_clip_mode);
-  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_SCAN)
+  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_SM_TILE)
     return fail(VTR_ERR_UNSUPPORTED, "unknown path %d", p->path);
   if ((p->d_values != nullptr) && !p->d_target_logits)
     return fail(VTR_ERR_INVALID_ARGUMENT, "d_values requires d_target_logits");
@@ -715,10 +1119,20 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     partials = static_cast<double*>(workspace);
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (int rc = vtr::run_column_path(p, partials, s)) return rc;
+  int num_partials = 0;
+  int rc = VTR_ERR_UNSUPPORTED;
+  const bool want_sm_tile = p->path == VTR_PATH_SM_TILE ||
+                            (p->path == VTR_PATH_AUTO && vtr::sm_tile_preferred(p));
+  if (p->path == VTR_PATH_SM_TILE && !vtr::sm_tile_eligible(p))
+    return fail(VTR_ERR_UNSUPPORTED,
+                "VTR_PATH_SM_TILE needs B %% 4 == 0 and 16-byte aligned tensors");
+  if (want_sm_tile) rc = vtr::run_sm_tile_path(p, partials, s, &num_partials);
+  if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE)
+    rc = vtr::run_column_path(p, partials, s, &num_partials);
+  if (rc) return rc;
   if (want_losses) {
-    return vtr_reduce_losses(partials, vtr::column_tiles(p->B), p->baseline_cost, p->entropy_cost,
-                             p->losses, p->losses_f64, stream);
+    return vtr_reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
+                             p->losses_f64, stream);
   }
   return VTR_OK;
 }

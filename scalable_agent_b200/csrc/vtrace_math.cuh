@@ -19,105 +19,141 @@ namespace vtr {
 namespace math {
 
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
 
-// exp(x) for x <= 0 on the MUFU pipe: 2^(x * log2 e).
-__device__ __forceinline__ float exp_nonpos(float x) { return ptx::ex2(__fmul_rn(x, kLog2e)); }
+// Softmax statistics of one logits row.
+struct RowStats {
+  float m;        // max_i x_i
+  float sum;      // sum_i e_i with e_i = 2^(x_i*log2e + c), c = fl(-m*log2e)
+  float ln_sum;   // log sum_i exp(x_i - m), i.e. logsumexp(x) - m
+};
+
+// The exponent offset c = fl(-m*log2e) lets each term cost one FMA + one MUFU.
+// Its rounding error is the same for every i, so it cancels in e_i / sum and
+// shows up in log(sum) as the constant (c_exact - c) * ln 2, which is added
+// back: ln_sum is as accurate as if x_i - m had been formed first.
+struct ExpOffset {
+  float c, ln_fix;
+  __device__ __forceinline__ explicit ExpOffset(float m) {
+    c = __fmul_rn(-m, kLog2e);
+    ln_fix = __fmul_rn(__fmaf_rn(-m, kLog2e, -c), kLn2);
+  }
+  __device__ __forceinline__ float term(float x) const { return ptx::ex2(__fmaf_rn(x, kLog2e, c)); }
+  __device__ __forceinline__ float ln_sum(float sum) const { return __fadd_rn(logf(sum), ln_fix); }
+};
 
 // ---- rows held in registers (A known at compile time) ----------------------
 
-// Behaviour row: returns sum_i exp(x_i - max), sets m = max.
 template <int N>
-__device__ __forceinline__ float row_exp_sum(const float (&x)[N], float& m) {
-  m = x[0];
+__device__ __forceinline__ float row_max(const float (&x)[N]) {
+  float m = x[0];
 #pragma unroll
   for (int i = 1; i < N; ++i) m = fmaxf(m, x[i]);
+  return m;
+}
+
+// Behaviour row: only the statistics are needed.
+template <int N>
+__device__ __forceinline__ RowStats row_stats(const float (&x)[N]) {
+  RowStats r;
+  r.m = row_max(x);
+  const ExpOffset off(r.m);
   float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
   for (int i = 0; i < N; ++i) {
-    const float v = exp_nonpos(__fsub_rn(x[i], m));
+    const float v = off.term(x[i]);
     if (i & 1) s1 = __fadd_rn(s1, v); else s0 = __fadd_rn(s0, v);
   }
-  return __fadd_rn(s0, s1);
+  r.sum = __fadd_rn(s0, s1);
+  r.ln_sum = off.ln_sum(r.sum);
+  return r;
 }
 
-// Target row: d <- x - max (d holds x on entry), ex <- exp(d); returns the sum.
+// Target row: also keeps the terms e_i (softmax p_i = e_i / sum).
 template <int N>
-__device__ __forceinline__ float row_exp_terms(float (&d)[N], float (&ex)[N], float& m) {
-  m = d[0];
-#pragma unroll
-  for (int i = 1; i < N; ++i) m = fmaxf(m, d[i]);
+__device__ __forceinline__ RowStats row_stats(const float (&x)[N], float (&e)[N]) {
+  RowStats r;
+  r.m = row_max(x);
+  const ExpOffset off(r.m);
   float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
   for (int i = 0; i < N; ++i) {
-    d[i] = __fsub_rn(d[i], m);
-    ex[i] = exp_nonpos(d[i]);
-    if (i & 1) s1 = __fadd_rn(s1, ex[i]); else s0 = __fadd_rn(s0, ex[i]);
+    e[i] = off.term(x[i]);
+    if (i & 1) s1 = __fadd_rn(s1, e[i]); else s0 = __fadd_rn(s0, e[i]);
   }
-  return __fadd_rn(s0, s1);
+  r.sum = __fadd_rn(s0, s1);
+  r.ln_sum = off.ln_sum(r.sum);
+  return r;
 }
 
-// ex <- softmax p, d <- log-softmax; returns the entropy H = -sum p log p
-// (experiment.py:332-334).
+// x <- log-softmax (x_i - logsumexp); returns the entropy H = -sum p log p
+// = -(sum_i e_i lp_i) / sum   (experiment.py:332-334).
 template <int N>
-__device__ __forceinline__ float row_entropy(float (&d)[N], float (&ex)[N], float inv_sum, float ln_sum) {
+__device__ __forceinline__ float row_entropy(float (&x)[N], const float (&e)[N], const RowStats& r,
+                                             float inv_sum) {
+  const float lse = __fadd_rn(r.m, r.ln_sum);
   float h0 = 0.0f, h1 = 0.0f;
 #pragma unroll
   for (int i = 0; i < N; ++i) {
-    ex[i] = __fmul_rn(ex[i], inv_sum);
-    d[i] = __fsub_rn(d[i], ln_sum);
-    if (i & 1) h1 = __fmaf_rn(-ex[i], d[i], h1); else h0 = __fmaf_rn(-ex[i], d[i], h0);
+    x[i] = __fsub_rn(x[i], lse);
+    if (i & 1) h1 = __fmaf_rn(e[i], x[i], h1); else h0 = __fmaf_rn(e[i], x[i], h0);
   }
-  return __fadd_rn(h0, h1);
+  return __fmul_rn(-inv_sum, __fadd_rn(h0, h1));
 }
 
-// ex <- p * (entropy_cost * log p + k), k = pg_adv + entropy_cost * H: the
-// gradient row but for the -onehot(a) * pg_adv term.
+// e <- p_i (entropy_cost lp_i + k) = e_i (ka lp_i + kb) with ka = ec/sum,
+// kb = k/sum, k = pg_adv + entropy_cost H: the gradient row but for the
+// -onehot(a) pg_adv term.
 template <int N>
-__device__ __forceinline__ void row_gradient(float (&ex)[N], const float (&d)[N], float ec, float k) {
+__device__ __forceinline__ void row_gradient(float (&e)[N], const float (&lp)[N], float ka, float kb) {
 #pragma unroll
-  for (int i = 0; i < N; ++i) ex[i] = __fmul_rn(ex[i], __fmaf_rn(ec, d[i], k));
+  for (int i = 0; i < N; ++i) e[i] = __fmul_rn(e[i], __fmaf_rn(ka, lp[i], kb));
 }
 
 // ---- rows left in shared memory (A known only at run time) ------------------
 // Same operations in the same order as the register versions above.
 
-__device__ __forceinline__ float smem_row_exp_sum(const float* row, int A, float& m) {
-  m = row[0];
-  for (int i = 1; i < A; ++i) m = fmaxf(m, row[i]);
+__device__ __forceinline__ RowStats smem_row_stats(const float* row, int A) {
+  RowStats r;
+  r.m = row[0];
+  for (int i = 1; i < A; ++i) r.m = fmaxf(r.m, row[i]);
+  const ExpOffset off(r.m);
   float s0 = 0.0f, s1 = 0.0f;
   for (int i = 0; i < A; ++i) {
-    const float v = exp_nonpos(__fsub_rn(row[i], m));
+    const float v = off.term(row[i]);
     if (i & 1) s1 = __fadd_rn(s1, v); else s0 = __fadd_rn(s0, v);
   }
-  return __fadd_rn(s0, s1);
+  r.sum = __fadd_rn(s0, s1);
+  r.ln_sum = off.ln_sum(r.sum);
+  return r;
 }
 
-__device__ __forceinline__ float smem_row_entropy(const float* row, int A, float m, float inv_sum,
-                                                  float ln_sum) {
+__device__ __forceinline__ float smem_row_entropy(const float* row, int A, const RowStats& r,
+                                                  float inv_sum) {
+  const ExpOffset off(r.m);
+  const float lse = __fadd_rn(r.m, r.ln_sum);
   float h0 = 0.0f, h1 = 0.0f;
   for (int i = 0; i < A; ++i) {
-    const float d = __fsub_rn(row[i], m);
-    const float p = __fmul_rn(exp_nonpos(d), inv_sum);
-    const float lp = __fsub_rn(d, ln_sum);
-    if (i & 1) h1 = __fmaf_rn(-p, lp, h1); else h0 = __fmaf_rn(-p, lp, h0);
+    const float e = off.term(row[i]);
+    const float lp = __fsub_rn(row[i], lse);
+    if (i & 1) h1 = __fmaf_rn(e, lp, h1); else h0 = __fmaf_rn(e, lp, h0);
   }
-  return __fadd_rn(h0, h1);
+  return __fmul_rn(-inv_sum, __fadd_rn(h0, h1));
 }
 
-__device__ __forceinline__ void smem_row_gradient(float* out, const float* row, int A, float m,
-                                                  float inv_sum, float ln_sum, float ec, float k) {
-  for (int i = 0; i < A; ++i) {
-    const float d = __fsub_rn(row[i], m);
-    const float p = __fmul_rn(exp_nonpos(d), inv_sum);
-    out[i] = __fmul_rn(p, __fmaf_rn(ec, __fsub_rn(d, ln_sum), k));
-  }
+__device__ __forceinline__ void smem_row_gradient(float* out, const float* row, int A,
+                                                  const RowStats& r, float ka, float kb) {
+  const ExpOffset off(r.m);
+  const float lse = __fadd_rn(r.m, r.ln_sum);
+  for (int i = 0; i < A; ++i)
+    out[i] = __fmul_rn(off.term(row[i]), __fmaf_rn(ka, __fsub_rn(row[i], lse), kb));
 }
 
 // ---- per-step scalars --------------------------------------------------------
 
 // log pi(a) = (x_a - max) - log sum exp(x - max)   (vtrace.py:67)
-__device__ __forceinline__ float action_log_prob(float x_a, float m, float ln_sum) {
-  return __fsub_rn(__fsub_rn(x_a, m), ln_sum);
+__device__ __forceinline__ float action_log_prob(float x_a, const RowStats& r) {
+  return __fsub_rn(__fsub_rn(x_a, r.m), r.ln_sum);
 }
 
 // experiment.py:377-382

@@ -204,11 +204,47 @@ def test_from_logits_vs_reference_ground_truth(api, golden, case):
     (7, 65, 5), (40, 37, 7), (9, 100, 32), (6, 34, 100), (4, 3, 256),
     (50, 130, 9), (100, 70, 18),
 ])
-@pytest.mark.parametrize('path', ['column'])
+@pytest.mark.parametrize('path', ['column', 'auto'])
 def test_fused_matches_oracle(api, T, B, A, path):
   _, experiment = api
   inp = oracle.synthetic_inputs(T, B, A, seed=T * 1000 + B + A)
   _check_fused(experiment, inp, path=path)
+
+
+@pytest.mark.parametrize('T,B,A', [
+    (5, 4, 3), (100, 32, 9), (20, 512, 18), (1, 4, 1), (2, 8, 4), (3, 64, 6),
+    (7, 68, 5), (40, 36, 7), (9, 100, 32), (6, 36, 100), (4, 4, 256),
+    (50, 132, 9), (100, 1000, 18), (100, 4736, 18), (30, 9000, 9),
+    (17, 38000, 18),
+])
+def test_sm_tile_kernel_matches_oracle(api, T, B, A):
+  """K1c explicitly (B % 4 == 0): every grid shape of its launch heuristics --
+  fewer tiles than SMs, one tile per SM with 1..8 column groups, two waves."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T * 1000 + B + A)
+  _check_fused(experiment, inp, path='sm_tile')
+
+
+def test_kernels_agree_bitwise(api):
+  """Whatever kernel the heuristics pick, a column gets the same bits."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(60, 2048, 18, seed=77)
+  outs = {}
+  for path in ('column', 'sm_tile'):
+    args, out = _run_fused(experiment, inp, path=path)
+    out.total_loss.backward()
+    outs[path] = (out, args['target_policy_logits'].grad, args['values'].grad)
+  a, b = outs['column'], outs['sm_tile']
+  for f in a[0].vtrace_returns._fields:
+    assert torch.equal(getattr(a[0].vtrace_returns, f), getattr(b[0].vtrace_returns, f)), f
+  assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+
+
+def test_sm_tile_refuses_unaligned_batch(api):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(5, 6, 3, seed=1)
+  with pytest.raises(ValueError, match='VTR_PATH_SM_TILE'):
+    _run_fused(experiment, inp, path='sm_tile')
 
 
 @pytest.mark.parametrize('crho,cpg', [(None, None), (3.7, 2.2), (1.0, None),
@@ -227,6 +263,11 @@ def test_fused_reward_clipping_and_done(api):
   for mode in ('abs_one', 'soft_asymmetric'):
     _check_fused(experiment, inp, reward_clipping=mode, done_np=inp['done'],
                  discounting=0.97)
+  inp = oracle.synthetic_inputs(25, 68, 9, seed=22, reward_clipping=None)
+  inp['rewards'] = inp['raw_rewards']
+  for path in ('column', 'sm_tile'):
+    _check_fused(experiment, inp, reward_clipping='soft_asymmetric',
+                 done_np=inp['done'], discounting=0.97, path=path)
 
 
 def test_config3_dmlab30_large(api):
