@@ -235,7 +235,13 @@ class FusedCall(object):
     self.p = p
     self.inp = inp
     self.stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
-    self.launches_per_call = 2   # K1 fused_column_kernel + K3 reduce_losses_kernel
+    count = ctypes.c_int(0)
+    text = ctypes.create_string_buffer(512)
+    rc = self.lib.vtr_fused_describe(ctypes.byref(p), 1, ctypes.byref(count), text, 512)
+    if rc != 0:
+      _lib.check(rc, 'vtr_fused_describe')
+    self.launches_per_call = count.value     # kernels of this library per call
+    self.plan = text.value.decode().strip()
 
   def __call__(self):
     rc = self.lib.vtr_from_logits_fused_f32(
@@ -395,8 +401,7 @@ def run_gpu(args):
             'frac': achieved / peak, 'traffic': traffic,
             'peak_source': peak_src,
             'algorithmic_bytes_per_launch': alg,
-            'kernel': 'fused_column_kernel<18,true> (+ reduce_losses_kernel, '
-                      'inside the same event pair)',
+            'kernel': call.plan + ' (whole call inside the event pair)',
             'kernel_ms_mean': kernel_mean_ms,
             'kernel_ms_min': min(kernel_ms),
             'frac_of_nominal_8TBs': achieved / 8000.0},

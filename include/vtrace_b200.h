@@ -129,15 +129,25 @@ typedef struct vtr_fused_params {
   double* losses_f64; /* double[4], may be NULL */
 } vtr_fused_params;
 
-/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A):
-   the per-tile loss partials of the deterministic two-stage reduction.
-   Returns 0 on invalid sizes. */
+/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): a
+   64-byte header (tile cursor and finish ticket of the per-SM kernel; the
+   library zeroes it itself) followed by the loss partials of the deterministic
+   two-stage reduction, one double[3] per 32-column tile or per 4-column
+   granule depending on the kernel.  Returns 0 on invalid sizes. */
 size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A);
 
 /* The fused pass.  `workspace` must hold vtr_fused_workspace_bytes() bytes,
    8-byte aligned; it is required only when p->losses is set. */
 int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* workspace,
                               size_t workspace_bytes, void* stream);
+
+/* What vtr_from_logits_fused_f32 would launch for `p` on the current device,
+   without launching anything: stores the number of kernels in *num_kernels
+   and writes a one-line description (kernel names, grid, ring depth, shared
+   memory) to `text`.  `have_workspace` = whether a workspace would be passed.
+   Host-side only; for benchmarks and logs. */
+int vtr_fused_describe(const vtr_fused_params* p, int have_workspace, int* num_kernels,
+                       char* text, size_t text_bytes);
 
 /* Most batch columns the allocation-free entry point below accepts. */
 #define VTR_NOALLOC_MAX_B 262144

@@ -71,6 +71,9 @@ SIGNATURES = {
         (ctypes.c_int, [ctypes.POINTER(FusedParams), _P, _SZ, _P]),
     'vtr_from_logits_fused_noalloc_f32':
         (ctypes.c_int, [ctypes.POINTER(FusedParams), _P]),
+    'vtr_fused_describe':
+        (ctypes.c_int, [ctypes.POINTER(FusedParams), ctypes.c_int,
+                        ctypes.POINTER(ctypes.c_int), ctypes.c_char_p, _SZ]),
     'vtr_reduce_losses': (ctypes.c_int, [_P, _I32, _F, _F, _P, _P, _P]),
     'vtr_from_importance_weights_f32':
         (ctypes.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _U32, _F, _F,

@@ -21,6 +21,7 @@
 // partials in a fixed order.  No atomics.
 #include <math.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.h"
 #include "ptx.cuh"
@@ -52,7 +53,9 @@ struct FusedArgs {
   float* t_lp;
   float* d_logits;
   float* d_values;
-  double* partials;  // [tiles][3] or null
+  double* partials;  // loss partials, or null
+  float* losses;       // K1c only: final losses written by the last tile to finish
+  double* losses_f64;  // K1c only
 };
 
 constexpr int kColumnsPerTile = 32;
@@ -560,15 +563,92 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
 //   carry      per consumer warp 3 x 32 floats
 //   sums       per consumer warp 3 doubles
 // ---------------------------------------------------------------------------
-constexpr int kSmBarrierBytes = 384;
-constexpr int kSmMaxConsumerWarps = 16;
+constexpr int kSmBarrierBytes = 512;
+constexpr int kSmMaxConsumerWarps = 18;
+constexpr int kMaxSms = 256;
+
+// Measured streaming speed of every SM (columns x steps per ns, smoothed over
+// calls), written by K1c at the end of each tile and read at the start of the
+// next call to size the tiles.  SMs do not get equal shares of the memory
+// system (on B200 the spread between the fastest and the slowest SM under full
+// load is ~40 %, fixed by where the SM sits), so equal tiles leave the fast SMs
+// idle for the last quarter of the kernel.  Only the partition depends on
+// this table; every output value is independent of the partition.
+static __device__ float g_sm_speed[kMaxSms];
 
 struct SmTileArgs {
   FusedArgs f;
-  int groups;        // column groups (warps side by side) per tile
+  int groups;        // column groups (warps side by side) per tile = capacity / 32
   int relay;         // warps per column group, owning interleaved time steps
   int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
+  int num_sm;        // SMs of the device
+  int waves;         // tiles per SM (grid = num_sm * waves) when balancing
+  unsigned int* cursor;  // zeroed column cursor for speed-weighted tiles, or null
 };
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned int sm_id() {
+  unsigned int s;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
+  return s;
+}
+
+// Tile sizing with the speed table (warp 0 of every tile computes the same
+// numbers from the same table): SM s gets granules in proportion to its
+// speed, clamped to [0.8, 1.25] x the even share, plus what is needed for the
+// shares to cover the batch.  Returns this tile's share in granules; falls
+// back to the even share when a share would exceed `cap` granules.
+__device__ __forceinline__ int weighted_share(const SmTileArgs& args, int total_gran, int cap,
+                                              int lane, unsigned int my_sm) {
+  const int nsm = args.num_sm, grid = nsm * args.waves;
+  float v[kMaxSms / 32];
+  float sum = 0.0f;
+  int cnt = 0;
+#pragma unroll
+  for (int k = 0; k < kMaxSms / 32; ++k) {
+    const int s = lane + 32 * k;
+    v[k] = s < nsm ? g_sm_speed[s] : 0.0f;
+    if (v[k] > 0.0f) sum += v[k], ++cnt;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, off);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+  }
+  const float mean = cnt > 0 ? sum / cnt : 0.0f;
+  const float even = static_cast<float>(total_gran) / grid;
+  int total = 0, biggest = 0, mine = 0;
+#pragma unroll
+  for (int k = 0; k < kMaxSms / 32; ++k) {
+    const int s = lane + 32 * k;
+    if (s < nsm) {
+      float w = (mean > 0.0f && v[k] > 0.0f) ? v[k] / mean : 1.0f;
+      w = fminf(fmaxf(w, 0.8f), 1.25f);
+      const int share = static_cast<int>(w * even);
+      total += share;
+      biggest = max(biggest, share);
+      if (s == static_cast<int>(my_sm)) mine = share;
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    total += __shfl_xor_sync(0xffffffffu, total, off);
+    biggest = max(biggest, __shfl_xor_sync(0xffffffffu, biggest, off));
+    mine = max(mine, __shfl_xor_sync(0xffffffffu, mine, off));
+  }
+  // Shares were rounded down: hand the missing granules out evenly, the
+  // remainder to the lowest SM ids, so that the shares add up to the batch.
+  const int deficit = max(0, total_gran - total * args.waves);
+  const int add = deficit / grid, rem = deficit - add * grid;
+  const int bump_below = (rem + args.waves - 1) / args.waves;
+  if (biggest + add + 1 > cap || my_sm >= static_cast<unsigned int>(nsm))
+    return min(cap, (total_gran + grid - 1) / grid);
+  return mine + add + (static_cast<int>(my_sm) < bump_below ? 1 : 0);
+}
 
 template <int A_CT, bool GRADS>
 __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
@@ -583,17 +663,33 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
   const int consumers = NG * R;
   const int cols = 32 * NG;  // slot stride in columns
 
-  // this tile's column range: B/4 granules of 4 columns dealt evenly to the grid
-  const int total_gran = B >> 2, G = gridDim.x, c = blockIdx.x;
-  const int base = total_gran / G, rem = total_gran % G;
-  const int col0 = (c * base + min(c, rem)) * 4;
-  const int ncols = (base + (c < rem ? 1 : 0)) * 4;
+  // This tile's column range, in granules of 4 columns (16-byte rows).  With a
+  // cursor: speed-weighted shares handed out first come, first served.
+  // Without: B/4 granules dealt evenly by block index.
+  __shared__ int sh_range[2];
+  const int total_gran = B >> 2;
+  const unsigned long long t_begin = global_timer_ns();
+  if (args.cursor) {
+    if (warp == 0) {
+      const int share = weighted_share(args, total_gran, cols >> 2, lane, sm_id());
+      if (lane == 0) {
+        const unsigned int start = atomicAdd(args.cursor, static_cast<unsigned int>(share * 4));
+        sh_range[0] = static_cast<int>(min(start, static_cast<unsigned int>(B)));
+        sh_range[1] = max(0, min(share * 4, B - sh_range[0]));
+      }
+    }
+  } else if (threadIdx.x == 0) {
+    const int G = gridDim.x, c = blockIdx.x;
+    const int base = total_gran / G, rem = total_gran % G;
+    sh_range[0] = (c * base + min(c, rem)) * 4;
+    sh_range[1] = (base + (c < rem ? 1 : 0)) * 4;
+  }
 
   const int slot_floats = cols * (2 * A + 4);
   float* ring = reinterpret_cast<float*>(smem_raw + kSmBarrierBytes);
   float* staging = ring + static_cast<size_t>(depth) * slot_floats;
   float* carry_buf = staging + (GRADS ? consumers * args.staging_bufs * 32 * A : 0);
-  double* warp_sums = reinterpret_cast<double*>(carry_buf + consumers * 96);
+  double* lane_sums = reinterpret_cast<double*>(carry_buf + consumers * 96);  // [consumer][k][lane]
   const uint32_t full_bars = ptx::smem_u32(smem_raw);
   const uint32_t empty_bars = full_bars + 128u;
   const uint32_t carry_bars = full_bars + 256u;
@@ -609,10 +705,11 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
     ptx::fence_proxy_async();
   }
   __syncthreads();
+  const int col0 = sh_range[0], ncols = sh_range[1];
 
   if (warp == consumers) {
     // ---- producer: one lane keeps the ring full ----
-    if (lane == 0) {
+    if (lane == 0 && ncols > 0) {
       const uint64_t policy = ptx::policy_evict_first();
       const uint32_t logit_bytes = static_cast<uint32_t>(ncols) * A * 4u;
       const uint32_t oper_bytes = static_cast<uint32_t>(ncols) * 4u;
@@ -634,7 +731,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
         ptx::bulk_g2s(op + 3u * cols * 4u, a.values + e0, oper_bytes, bar, policy);
       }
     }
-  } else {
+  } else if (ncols > 0) {
     // ---- consumers ----
     const int g = warp % NG, r = warp / NG;
     const int j = 32 * g + lane;  // column within the tile
@@ -782,23 +879,70 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
     }
 
     if (a.partials) {
-      const double pg_sum = warp_sum_fixed(sums.pg);
-      const double bl_sum = warp_sum_fixed(sums.baseline);
-      const double ent_sum = warp_sum_fixed(sums.entropy);
-      if (lane == 0)
-        warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
+      double* mine = lane_sums + static_cast<size_t>(warp) * 96;
+      mine[lane] = sums.pg, mine[32 + lane] = sums.baseline, mine[64 + lane] = sums.entropy;
     }
     if (GRADS && lane == 0) ptx::bulk_wait<0>();
   }
 
   if (a.partials) {
+    // One partial per granule of 4 columns, summed over the relay warps and then
+    // over the 4 lanes in a fixed order: the same numbers however the batch
+    // was cut into tiles.
     __syncthreads();
-    if (threadIdx.x == 0) {
+    for (int q = threadIdx.x; q < (ncols >> 2); q += blockDim.x) {
+      const int g = (4 * q) >> 5, l0 = (4 * q) & 31;
+      double p[3] = {0.0, 0.0, 0.0};
+      for (int l = l0; l < l0 + 4; ++l)
+        for (int r = 0; r < R; ++r) {
+          const double* src = lane_sums + static_cast<size_t>(r * NG + g) * 96;
+          p[0] += src[l], p[1] += src[32 + l], p[2] += src[64 + l];
+        }
+      double* out = a.partials + 3 * (static_cast<size_t>(col0 >> 2) + q);
+      out[0] = p[0], out[1] = p[1], out[2] = p[2];
+    }
+  }
+  if (a.partials && args.cursor && (a.losses || a.losses_f64)) {
+    // Second stage inside the same launch: the tile that finishes last (a
+    // ticket, the only other atomic besides the cursor; no value is ever
+    // accumulated atomically) sums all granule partials in a fixed order.
+    __shared__ int sh_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) sh_last = atomicAdd(args.cursor + 1, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (sh_last) {
+      __threadfence();
+      const volatile double* parts = a.partials;
       double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int w = 0; w < consumers; ++w)
-        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
-      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
-      out[0] = p0, out[1] = p1, out[2] = p2;
+      for (int i = threadIdx.x; i < total_gran; i += blockDim.x)
+        p0 += parts[3 * i], p1 += parts[3 * i + 1], p2 += parts[3 * i + 2];
+      p0 = warp_sum_fixed(p0), p1 = warp_sum_fixed(p1), p2 = warp_sum_fixed(p2);
+      double* warp_tot = lane_sums;  // free again: every tile partial has been written
+      if (lane == 0) warp_tot[3 * warp] = p0, warp_tot[3 * warp + 1] = p1, warp_tot[3 * warp + 2] = p2;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double pg = 0.0, bl = 0.0, ent = 0.0;
+        for (int w = 0; w <= consumers; ++w)
+          pg += warp_tot[3 * w], bl += warp_tot[3 * w + 1], ent += warp_tot[3 * w + 2];
+        const double total = pg + static_cast<double>(a.baseline_cost) * bl +
+                             static_cast<double>(a.entropy_cost) * ent;
+        if (a.losses) {
+          a.losses[0] = static_cast<float>(pg), a.losses[1] = static_cast<float>(bl);
+          a.losses[2] = static_cast<float>(ent), a.losses[3] = static_cast<float>(total);
+        }
+        if (a.losses_f64)
+          a.losses_f64[0] = pg, a.losses_f64[1] = bl, a.losses_f64[2] = ent, a.losses_f64[3] = total;
+      }
+    }
+  }
+  if (threadIdx.x == 0 && ncols > 0) {
+    const unsigned int sm = sm_id();
+    const unsigned long long dt = global_timer_ns() - t_begin;
+    if (sm < kMaxSms && dt > 0) {
+      const float speed = static_cast<float>(ncols) * T / static_cast<float>(dt);
+      const float old = g_sm_speed[sm];
+      g_sm_speed[sm] = old > 0.0f ? 0.5f * (old + speed) : speed;
     }
   }
 }
@@ -839,8 +983,32 @@ __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __rest
 
 static inline int column_tiles(int B) { return (B + kColumnsPerTile - 1) / kColumnsPerTile; }
 
+// vtr_fused_describe(): the launch functions below record what they would
+// launch instead of launching it.
+struct PlanRecorder {
+  bool dry_run = false;
+  int kernels = 0;
+  char text[256] = "";
+};
+static thread_local PlanRecorder g_plan;
+
+static void record_plan(const char* fmt, ...) {
+  const size_t used = strlen(g_plan.text);
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_plan.text + used, sizeof(g_plan.text) - used, fmt, ap);
+  va_end(ap);
+  ++g_plan.kernels;
+}
+
 template <int A_CT, bool GRADS>
 static int launch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
+  if (g_plan.dry_run) {
+    record_plan("%s<A=%d,%s> grid=%d warps/tile=%d ring=%d smem=%zu; ",
+                warps > 1 ? "fused_relay_kernel" : "fused_column_kernel", A_CT, GRADS ? "grads" : "fwd",
+                tiles, warps, args.depth, smem);
+    return VTR_OK;
+  }
   auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
   VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       static_cast<int>(smem)));
@@ -895,6 +1063,7 @@ static void fill_args(FusedArgs& a, const vtr_fused_params* p, double* partials)
   a.b_lp = p->behaviour_action_log_probs, a.t_lp = p->target_action_log_probs;
   a.d_logits = p->d_target_logits, a.d_values = p->d_values;
   a.partials = partials;
+  a.losses = nullptr, a.losses_f64 = nullptr;
   a.depth = 0, a.slot_floats = 0, a.tma_in_ok = 0, a.tma_out_ok = 0;
 }
 
@@ -920,6 +1089,12 @@ static bool sm_tile_preferred(const vtr_fused_params* p) {
 
 template <int A_CT, bool GRADS>
 static int launch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStream_t stream) {
+  if (g_plan.dry_run) {
+    record_plan("fused_sm_tile_kernel<A=%d,%s> grid=%d groups=%d relay=%d ring=%d smem=%zu %s; ", A_CT,
+                GRADS ? "grads" : "fwd", grid, args.groups, args.relay, args.f.depth, smem,
+                args.cursor ? "speed-weighted tiles, in-kernel final reduction" : "even tiles");
+    return VTR_OK;
+  }
   auto kernel = fused_sm_tile_kernel<A_CT, GRADS>;
   VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       static_cast<int>(smem)));
@@ -940,37 +1115,62 @@ static int dispatch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaS
   }
 }
 
-// K1c launch: `*num_partials` = tiles written.  Returns VTR_ERR_UNSUPPORTED
-// without launching if the shape does not fit this kernel's shared memory.
-static int run_sm_tile_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
-                            int* num_partials) {
+// Workspace layout (vtr_fused_workspace_bytes): a 64-byte header whose first
+// word is K1c's column cursor, then the loss partials.
+constexpr size_t kWorkspaceHeaderBytes = 64;
+
+// K1c launch: `*num_partials` = partials written (one per granule of 4 columns).
+// `header` is the 64-byte workspace header, or null when the caller gave no
+// workspace (then tiles are dealt evenly instead of by measured SM speed).
+// Returns VTR_ERR_UNSUPPORTED without launching if the shape does not fit this
+// kernel's shared memory.
+static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* partials,
+                            cudaStream_t stream, int* num_partials, bool* losses_done) {
   DeviceInfo dev;
   if (int rc = device_info(&dev)) return rc;
   const bool grads = p->d_target_logits != nullptr;
   const int sm = dev.sm_count;
   const int total_gran = p->B / 4;
 
-  // Grid: equal column ranges; a multiple of the SM count once the batch is
-  // wide enough to give every SM at least one 32-column group.
+  // Grid: a multiple of the SM count once the batch is wide enough to give
+  // every SM at least one 32-column group; tiles of at most ~256 columns.
   int waves = 1, grid;
   if (p->B < 32 * sm) {
     grid = (p->B + 31) / 32;
   } else {
-    waves = (p->B + sm * 256 - 1) / (sm * 256);
+    waves = (p->B + sm * 224 - 1) / (sm * 224);
     grid = sm * waves;
   }
-  const int ncols_max = ((total_gran + grid - 1) / grid) * 4;
+  const bool balance = header != nullptr && grid % sm == 0 && sm <= kMaxSms &&
+                       !getenv("VTR_SM_NO_BALANCE");
+  const int even_cols = ((total_gran + grid - 1) / grid) * 4;
+  // Tile capacity: the even share, or with balancing 1.25x + 2 granules of it
+  // (weighted_share clamps to 1.25x and adds at most a couple of granules).
+  int cap_cols = even_cols;
+  if (balance) {
+    int headroom = env_int("VTR_SM_HEADROOM");  // percent, experiments only
+    if (headroom <= 0) headroom = 25;
+    cap_cols = even_cols + even_cols * headroom / 100 + 8;
+  }
   SmTileArgs args;
   fill_args(args.f, p, partials);
-  args.groups = (ncols_max + 31) / 32;
+  args.groups = (cap_cols + 31) / 32;
+  args.num_sm = sm;
+  args.waves = waves;
+  args.cursor = balance ? static_cast<unsigned int*>(header) : nullptr;
+  if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
+  *losses_done = balance;
 
   // Consumer warps: ~16 per SM.  Two tiles share an SM when the batch needs
   // two or more waves, so that the waves overlap instead of queueing.
   const int co_resident = waves >= 2 ? 2 : 1;
-  int relay = kSmMaxConsumerWarps / co_resident / args.groups;
+  const int max_consumers = kSmMaxConsumerWarps / co_resident;
+  if (args.groups > max_consumers) return fail(VTR_ERR_UNSUPPORTED, "sm-tile kernel: tile too wide");
+  int relay = max(1, max_consumers / args.groups);
+  if (relay * args.groups > 16 / co_resident && relay > 2) relay = max(2, 16 / co_resident / args.groups);
   if (const int forced = env_int("VTR_SM_RELAY")) relay = forced;
   if (relay > p->T) relay = p->T;
-  if (relay * args.groups > kSmMaxConsumerWarps) relay = kSmMaxConsumerWarps / args.groups;
+  if (relay * args.groups > max_consumers) relay = max_consumers / args.groups;
   if (relay < 1) relay = 1;
 
   size_t budget = static_cast<size_t>(dev.smem_per_sm) / co_resident;
@@ -985,7 +1185,7 @@ static int run_sm_tile_path(const vtr_fused_params* p, double* partials, cudaStr
     args.staging_bufs = relay == 1 ? 2 : 1;
     fixed = kSmBarrierBytes + args.groups * relay *
                                   ((grads ? args.staging_bufs * row : 0) + 96 * sizeof(float) +
-                                   3 * sizeof(double));
+                                   96 * sizeof(double));
     depth = budget > fixed ? static_cast<long>((budget - fixed) / slot_bytes) : 0;
     if (const int forced = env_int("VTR_COLUMN_DEPTH")) depth = forced;
     if (depth > kMaxDepth) depth = kMaxDepth;
@@ -999,7 +1199,9 @@ static int run_sm_tile_path(const vtr_fused_params* p, double* partials, cudaStr
   if (depth < 1) depth = 1;
   args.f.depth = static_cast<int>(depth);
   const size_t smem = fixed + depth * slot_bytes;
-  *num_partials = grid;
+  if (balance && !g_plan.dry_run)
+    VTR_CUDA_CHECK(cudaMemsetAsync(header, 0, kWorkspaceHeaderBytes, stream));
+  *num_partials = total_gran;
   return grads ? dispatch_sm_tile<true>(args, grid, smem, stream)
                : dispatch_sm_tile<false>(args, grid, smem, stream);
 }
@@ -1068,7 +1270,10 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
 
 extern "C" size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A) {
   if (T <= 0 || B <= 0 || A <= 0) return 0;
-  return static_cast<size_t>(vtr::column_tiles(B)) * 3 * sizeof(double);
+  // header + one double[3] per 32-column tile (K1a/K1b) or per 4-column granule (K1c)
+  const size_t partials = static_cast<size_t>(vtr::column_tiles(B)) > static_cast<size_t>(B / 4)
+                              ? vtr::column_tiles(B) : B / 4;
+  return vtr::kWorkspaceHeaderBytes + partials * 3 * sizeof(double);
 }
 
 extern "C" int vtr_reduce_losses(const double* partials, int32_t num_partials,
@@ -1076,6 +1281,10 @@ extern "C" int vtr_reduce_losses(const double* partials, int32_t num_partials,
                                  double* losses_f64, void* stream) {
   if (!partials || num_partials <= 0) return vtr::fail(VTR_ERR_INVALID_ARGUMENT, "vtr_reduce_losses: no partials");
   if (!losses && !losses_f64) return vtr::fail(VTR_ERR_INVALID_ARGUMENT, "vtr_reduce_losses: no output");
+  if (vtr::g_plan.dry_run) {
+    vtr::record_plan("reduce_losses_kernel grid=1 partials=%d; ", num_partials);
+    return VTR_OK;
+  }
   vtr::reduce_losses_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       partials, num_partials, baseline_cost, entropy_cost, losses, losses_f64);
   VTR_CUDA_CHECK(cudaGetLastError());
@@ -1112,11 +1321,14 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   const bool want_losses = p->losses || p->losses_f64;
   double* partials = nullptr;
   if (want_losses) {
-    const size_t need = vtr_fused_workspace_bytes(p->T, p->B, p->A);
+    // K1a/K1b write one partial per 32-column tile, K1c one per 4-column granule.
+    const size_t need = p->path == VTR_PATH_COLUMN
+                            ? vtr::kWorkspaceHeaderBytes + vtr::column_tiles(p->B) * 3 * sizeof(double)
+                            : vtr_fused_workspace_bytes(p->T, p->B, p->A);
     if (!workspace || workspace_bytes < need)
       return fail(VTR_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
     if (!vtr::aligned(workspace, 8)) return fail(VTR_ERR_MISALIGNED, "workspace is not 8-byte aligned");
-    partials = static_cast<double*>(workspace);
+    partials = reinterpret_cast<double*>(static_cast<char*>(workspace) + vtr::kWorkspaceHeaderBytes);
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   int num_partials = 0;
@@ -1126,14 +1338,35 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   if (p->path == VTR_PATH_SM_TILE && !vtr::sm_tile_eligible(p))
     return fail(VTR_ERR_UNSUPPORTED,
                 "VTR_PATH_SM_TILE needs B %% 4 == 0 and 16-byte aligned tensors");
-  if (want_sm_tile) rc = vtr::run_sm_tile_path(p, partials, s, &num_partials);
-  if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE)
+  bool losses_done = false;
+  if (want_sm_tile)
+    rc = vtr::run_sm_tile_path(p, want_losses ? workspace : nullptr, partials, s, &num_partials,
+                               &losses_done);
+  if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE) {
+    losses_done = false;
     rc = vtr::run_column_path(p, partials, s, &num_partials);
+  }
   if (rc) return rc;
-  if (want_losses) {
+  if (want_losses && !losses_done) {
     return vtr_reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
                              p->losses_f64, stream);
   }
+  return VTR_OK;
+}
+
+extern "C" int vtr_fused_describe(const vtr_fused_params* p, int have_workspace, int* num_kernels,
+                                  char* text, size_t text_bytes) {
+  vtr::g_plan = vtr::PlanRecorder();
+  vtr::g_plan.dry_run = true;
+  // Validation wants a workspace pointer when losses are requested; nothing is
+  // written through it in a dry run.
+  static double dummy[8];
+  const int rc = vtr_from_logits_fused_f32(p, have_workspace ? dummy : nullptr,
+                                           have_workspace ? static_cast<size_t>(-1) : 0, nullptr);
+  vtr::g_plan.dry_run = false;
+  if (rc != VTR_OK) return rc;
+  if (text && text_bytes) snprintf(text, text_bytes, "%s", vtr::g_plan.text);
+  if (num_kernels) *num_kernels = vtr::g_plan.kernels;
   return VTR_OK;
 }
 
@@ -1155,7 +1388,8 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
 namespace vtr {
 
 constexpr int kNoAllocMaxTiles = VTR_NOALLOC_MAX_B / kColumnsPerTile;
-static __device__ __align__(256) double g_noalloc_partials[kNoAllocMaxTiles * 3];
+constexpr size_t kNoAllocDoubles = kWorkspaceHeaderBytes / sizeof(double) + kNoAllocMaxTiles * 3;
+static __device__ __align__(256) double g_noalloc_partials[kNoAllocDoubles];
 
 // In host code `g_noalloc_partials` only names the symbol; the address the
 // kernels can use is per device and comes from cudaGetSymbolAddress, asked
@@ -1189,8 +1423,14 @@ extern "C" int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void
                      p->B, VTR_NOALLOC_MAX_B);
   double* scratch = nullptr;
   if (int rc = vtr::noalloc_scratch(&scratch)) return rc;
-  // Nothing in the scratch has to start at zero: the first stage writes the
-  // partial of every tile the second stage reads, so whatever an earlier call
-  // left behind is overwritten or never looked at.
-  return vtr_from_logits_fused_f32(p, scratch, sizeof(double) * 3 * vtr::kNoAllocMaxTiles, stream);
+  // The scratch is sized for one partial per 32-column tile, so this entry
+  // point always takes the 32-column-tile kernels unless the caller asked for
+  // a specific one.  Nothing in it has to start at zero on that path: the first
+  // stage writes the partial of every tile the second stage reads, so whatever
+  // an earlier call left behind is overwritten or never looked at.  (The
+  // per-SM kernel keeps a cursor in the scratch header; the library zeroes it
+  // itself before every launch that uses it.)
+  vtr_fused_params q = *p;
+  if (q.path == VTR_PATH_AUTO) q.path = VTR_PATH_COLUMN;
+  return vtr_from_logits_fused_f32(&q, scratch, sizeof(double) * vtr::kNoAllocDoubles, stream);
 }
