@@ -60,6 +60,7 @@ extern "C" {
 #define VTR_PATH_AUTO 0
 #define VTR_PATH_COLUMN 1  /* 32-column tiles, one ring per tile (any alignment) */
 #define VTR_PATH_SM_TILE 2 /* one wide tile per SM, shared ring (16-B aligned)  */
+#define VTR_PATH_ITEM 3    /* one thread per (t, b) item: small B, T <= 256      */
 
 int vtr_version(void);
 

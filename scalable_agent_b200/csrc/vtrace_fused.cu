@@ -947,6 +947,139 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
   }
 }
 
+// ---------------------------------------------------------------------------
+// K2: item-parallel kernel for small batches.  One CTA per batch column, one
+// thread per time step: every thread loads its own two logits rows straight
+// from global memory, does everything that does not depend on step t+1, and
+// leaves (gain_t, delta_t) in shared memory; thread 0 then runs the recurrence
+// acc_t = gain_t acc_{t+1} + delta_t over the T entries (T dependent FMAs, a
+// fraction of a microsecond) and every thread finishes its own step.  The
+// arithmetic is the same sequence of operations as in K1, so the results are
+// bit-identical to K1's.  With B columns x T steps all in flight at once, a
+// small batch costs one memory round trip instead of T sequential steps.
+// Needs T <= kItemMaxSteps and a compile-time A.
+// ---------------------------------------------------------------------------
+constexpr int kItemMaxSteps = 256;
+constexpr int kItemMaxColumns = 16384;  // K2 writes one loss partial per column
+
+template <int N>
+__device__ __forceinline__ void load_row_global(float (&x)[N], const float* row) {
+  if (N % 2 == 0 && (reinterpret_cast<uintptr_t>(row) & 7) == 0) {
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(row) + i);
+      x[2 * i] = v.x, x[2 * i + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; ++i) x[i] = __ldg(row + i);
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void store_row_global(float* row, const float (&x)[N]) {
+  if (N % 2 == 0 && (reinterpret_cast<uintptr_t>(row) & 7) == 0) {
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) reinterpret_cast<float2*>(row)[i] = make_float2(x[2 * i], x[2 * i + 1]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; ++i) row[i] = x[i];
+  }
+}
+
+template <int A_CT, bool GRADS>
+__global__ void __launch_bounds__(kItemMaxSteps) fused_item_kernel(const __grid_constant__ FusedArgs a) {
+  static_assert(A_CT > 0, "the item kernel keeps rows in registers");
+  __shared__ float sh_gain[kItemMaxSteps], sh_delta[kItemMaxSteps], sh_acc[kItemMaxSteps];
+  __shared__ double sh_sums[3][kItemMaxSteps / 32];
+  const int T = a.T, B = a.B;
+  const int k = threadIdx.x;  // step index from the end: t = T-1-k
+  const int b = blockIdx.x;
+  const bool active = k < T;
+  const int t = T - 1 - (active ? k : 0);
+  const size_t e = static_cast<size_t>(t) * B + b;
+  const bool need_softmax = GRADS || a.partials != nullptr;
+
+  float disc = 0.0f, rew = 0.0f, val = 0.0f, v_next = 0.0f, t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
+  float entropy = 0.0f, inv_sum = 0.0f;
+  int act = 0;
+  math::Weights w = {0.0f, 0.0f, 0.0f};
+  float x[A_CT], ex[A_CT];
+  if (active) {
+    act = min(max(__ldg(a.actions + e), 0), A_CT - 1);
+    disc = a.done ? (a.done[e] ? 0.0f : a.discounting) : __ldg(a.discounts + e);
+    rew = math::clip_reward(__ldg(a.rewards + e), a.reward_clip_mode);
+    val = __ldg(a.values + e);
+    v_next = k == 0 ? __ldg(a.bootstrap + b) : __ldg(a.values + e + B);  // vtrace.py:243-244
+    float xb[A_CT];
+    load_row_global(xb, a.blog + e * A_CT);
+    load_row_global(x, a.tlog + e * A_CT);
+    const float xa_b = __ldg(a.blog + e * A_CT + act), xa_t = __ldg(a.tlog + e * A_CT + act);
+    const math::RowStats sb = math::row_stats(xb);
+    const math::RowStats st = math::row_stats(x, ex);
+    t_lp = math::action_log_prob(xa_t, st);
+    b_lp = math::action_log_prob(xa_b, sb);
+    log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
+    w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
+    if (need_softmax) {
+      inv_sum = __frcp_rn(st.sum);
+      entropy = math::row_entropy(x, ex, st, inv_sum);
+    }
+    sh_gain[k] = math::step_gain(w, disc);
+    sh_delta[k] = math::step_delta(w, rew, disc, val, v_next);
+  }
+  __syncthreads();
+  if (k == 0) {
+    float acc = 0.0f;  // vtrace.py:256
+    for (int i = 0; i < T; ++i) {
+      acc = math::step_acc(sh_gain[i], acc, sh_delta[i]);
+      sh_acc[i] = acc;
+    }
+  }
+  __syncthreads();
+
+  double s_pg = 0.0, s_bl = 0.0, s_ent = 0.0;
+  if (active) {
+    const float vs = __fadd_rn(sh_acc[k], val);  // vtrace.py:265
+    // vs_{t+1} = acc_{t+1} + V(x_{t+1}); bootstrap_value past the end (:268-269)
+    const float vs_next = k == 0 ? v_next : __fadd_rn(sh_acc[k - 1], v_next);
+    const float pg = math::step_pg(w, rew, disc, val, vs_next);
+    if (a.vs) a.vs[e] = vs;
+    if (a.pg) a.pg[e] = pg;
+    if (a.log_rhos) a.log_rhos[e] = log_rho;
+    if (a.b_lp) a.b_lp[e] = b_lp;
+    if (a.t_lp) a.t_lp[e] = t_lp;
+    if (GRADS) {
+      const float ka = __fmul_rn(a.entropy_cost, inv_sum);
+      const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
+      math::row_gradient(ex, x, ka, kb);
+#pragma unroll
+      for (int i = 0; i < A_CT; ++i)
+        if (i == act) ex[i] = __fsub_rn(ex[i], pg);  // the -onehot(a) * pg_adv term
+      store_row_global(a.d_logits + e * A_CT, ex);
+      if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
+    }
+    if (a.partials) {
+      math::LossSums one = {0.0, 0.0, 0.0};
+      one.add(t_lp, pg, vs, val, entropy);
+      s_pg = one.pg, s_bl = one.baseline, s_ent = one.entropy;
+    }
+  }
+  if (a.partials) {
+    // fixed order: xor tree inside each warp, then the warps in index order
+    s_pg = warp_sum_fixed(s_pg), s_bl = warp_sum_fixed(s_bl), s_ent = warp_sum_fixed(s_ent);
+    if ((k & 31) == 0) sh_sums[0][k >> 5] = s_pg, sh_sums[1][k >> 5] = s_bl, sh_sums[2][k >> 5] = s_ent;
+    __syncthreads();
+    if (k == 0) {
+      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+      for (int wi = 0; wi < (blockDim.x >> 5); ++wi)
+        p0 += sh_sums[0][wi], p1 += sh_sums[1][wi], p2 += sh_sums[2][wi];
+      double* out = a.partials + 3 * static_cast<size_t>(b);
+      out[0] = p0, out[1] = p1, out[2] = p2;
+    }
+  }
+}
+
 // K3: second stage of the loss reduction.  One block, fixed summation order.
 __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __restrict__ partials,
                                                             int n, float baseline_cost,
@@ -982,6 +1115,8 @@ __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __rest
 }
 
 static inline int column_tiles(int B) { return (B + kColumnsPerTile - 1) / kColumnsPerTile; }
+
+static bool specialised_actions(int A) { return A == 3 || A == 4 || A == 6 || A == 9 || A == 18; }
 
 // vtr_fused_describe(): the launch functions below record what they would
 // launch instead of launching it.
@@ -1206,6 +1341,52 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
                : dispatch_sm_tile<false>(args, grid, smem, stream);
 }
 
+// VTR_PATH_AUTO takes K2 for the smallest batches only: its threads read their
+// rows straight from global memory, 72-byte pieces 2 MB apart, which is fine
+// for a few hundred columns and slower than K1b's ring beyond (measured at
+// T=100 A=18: B=256 14 us vs 25 us, B=512 20 us vs 25 us, B=1024 29 us vs 26 us,
+// B=2048 50 us vs 23 us).
+constexpr int kItemAutoColumns = 512;
+static bool item_kernel_applies(const vtr_fused_params* p) {
+  return p->T <= kItemMaxSteps && specialised_actions(p->A) && p->B <= kItemAutoColumns;
+}
+
+template <int A_CT, bool GRADS>
+static int launch_item(const FusedArgs& args, cudaStream_t stream) {
+  const int threads = ((args.T + 31) / 32) * 32;
+  if (g_plan.dry_run) {
+    record_plan("fused_item_kernel<A=%d,%s> grid=%d threads=%d; ", A_CT, GRADS ? "grads" : "fwd", args.B,
+                threads);
+    return VTR_OK;
+  }
+  fused_item_kernel<A_CT, GRADS><<<args.B, threads, 0, stream>>>(args);
+  VTR_CUDA_CHECK(cudaGetLastError());
+  return VTR_OK;
+}
+
+template <bool GRADS>
+static int dispatch_item(const FusedArgs& args, cudaStream_t stream) {
+  switch (args.A) {
+    case 3: return launch_item<3, GRADS>(args, stream);
+    case 4: return launch_item<4, GRADS>(args, stream);
+    case 6: return launch_item<6, GRADS>(args, stream);
+    case 9: return launch_item<9, GRADS>(args, stream);
+    case 18: return launch_item<18, GRADS>(args, stream);
+    default: return fail(VTR_ERR_UNSUPPORTED, "item kernel: A=%d is not a compiled-in size", args.A);
+  }
+}
+
+static int run_item_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
+                         int* num_partials) {
+  if (p->T > kItemMaxSteps || p->B > kItemMaxColumns)
+    return fail(VTR_ERR_UNSUPPORTED, "item kernel: needs T <= %d and B <= %d", kItemMaxSteps,
+                kItemMaxColumns);
+  FusedArgs a;
+  fill_args(a, p, partials);
+  *num_partials = p->B;  // one partial per column
+  return p->d_target_logits ? dispatch_item<true>(a, stream) : dispatch_item<false>(a, stream);
+}
+
 static int run_column_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
                            int* num_partials) {
   DeviceInfo dev;
@@ -1270,9 +1451,11 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
 
 extern "C" size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A) {
   if (T <= 0 || B <= 0 || A <= 0) return 0;
-  // header + one double[3] per 32-column tile (K1a/K1b) or per 4-column granule (K1c)
-  const size_t partials = static_cast<size_t>(vtr::column_tiles(B)) > static_cast<size_t>(B / 4)
-                              ? vtr::column_tiles(B) : B / 4;
+  // header + one double[3] per 32-column tile (K1a/K1b), per 4-column granule
+  // (K1c) or per column (K2, which only runs below kItemMaxColumns columns)
+  size_t partials = static_cast<size_t>(vtr::column_tiles(B));
+  if (static_cast<size_t>(B / 4) > partials) partials = B / 4;
+  if (B <= vtr::kItemMaxColumns && static_cast<size_t>(B) > partials) partials = B;
   return vtr::kWorkspaceHeaderBytes + partials * 3 * sizeof(double);
 }
 
@@ -1306,7 +1489,7 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     return fail(VTR_ERR_INVALID_ARGUMENT, "one of discounts / done must be given");
   if (p->reward_clip_mode < VTR_REWARD_CLIP_NONE || p->reward_clip_mode > VTR_REWARD_CLIP_SOFT_ASYMMETRIC)
     return fail(VTR_ERR_UNSUPPORTED, "unknown reward_clip_mode %d", p->reward_clip_mode);
-  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_SM_TILE)
+  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_ITEM)
     return fail(VTR_ERR_UNSUPPORTED, "unknown path %d", p->path);
   if ((p->d_values != nullptr) && !p->d_target_logits)
     return fail(VTR_ERR_INVALID_ARGUMENT, "d_values requires d_target_logits");
@@ -1325,6 +1508,8 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     const size_t need = p->path == VTR_PATH_COLUMN
                             ? vtr::kWorkspaceHeaderBytes + vtr::column_tiles(p->B) * 3 * sizeof(double)
                             : vtr_fused_workspace_bytes(p->T, p->B, p->A);
+    if (p->path == VTR_PATH_ITEM && p->B > vtr::kItemMaxColumns)
+      return fail(VTR_ERR_UNSUPPORTED, "VTR_PATH_ITEM needs B <= %d", vtr::kItemMaxColumns);
     if (!workspace || workspace_bytes < need)
       return fail(VTR_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
     if (!vtr::aligned(workspace, 8)) return fail(VTR_ERR_MISALIGNED, "workspace is not 8-byte aligned");
@@ -1344,7 +1529,10 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
                                &losses_done);
   if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE) {
     losses_done = false;
-    rc = vtr::run_column_path(p, partials, s, &num_partials);
+    if (p->path == VTR_PATH_ITEM || (p->path == VTR_PATH_AUTO && vtr::item_kernel_applies(p)))
+      rc = vtr::run_item_path(p, partials, s, &num_partials);
+    else
+      rc = vtr::run_column_path(p, partials, s, &num_partials);
   }
   if (rc) return rc;
   if (want_losses && !losses_done) {
@@ -1423,14 +1611,17 @@ extern "C" int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void
                      p->B, VTR_NOALLOC_MAX_B);
   double* scratch = nullptr;
   if (int rc = vtr::noalloc_scratch(&scratch)) return rc;
-  // The scratch is sized for one partial per 32-column tile, so this entry
-  // point always takes the 32-column-tile kernels unless the caller asked for
-  // a specific one.  Nothing in it has to start at zero on that path: the first
-  // stage writes the partial of every tile the second stage reads, so whatever
-  // an earlier call left behind is overwritten or never looked at.  (The
-  // per-SM kernel keeps a cursor in the scratch header; the library zeroes it
-  // itself before every launch that uses it.)
+  // The scratch holds one partial per 32-column tile of the largest batch.  The
+  // other kernels write more partials per column, so they are only eligible
+  // while their workspace still fits; beyond that this entry point takes the
+  // 32-column-tile kernels.  The partials never have to start at zero: the
+  // first stage writes every one the second stage reads, so whatever an
+  // earlier call left behind is overwritten or never looked at.  The per-SM
+  // kernel keeps a cursor in the scratch header; the library zeroes that
+  // itself before every launch that uses it.
+  const size_t scratch_bytes = sizeof(double) * vtr::kNoAllocDoubles;
   vtr_fused_params q = *p;
-  if (q.path == VTR_PATH_AUTO) q.path = VTR_PATH_COLUMN;
-  return vtr_from_logits_fused_f32(&q, scratch, sizeof(double) * vtr::kNoAllocDoubles, stream);
+  if (q.path == VTR_PATH_AUTO && vtr_fused_workspace_bytes(q.T, q.B, q.A) > scratch_bytes)
+    q.path = VTR_PATH_COLUMN;
+  return vtr_from_logits_fused_f32(&q, scratch, scratch_bytes, stream);
 }

@@ -189,13 +189,32 @@ struct Carry {
   float vs_next;  // vs_{t+1};   bootstrap_value past the end (vtrace.py:268-269)
 };
 
-// One step of the reverse scan (vtrace.py:245-276); updates the carry.
+// The pieces of one step of the reverse scan (vtrace.py:245-276).  Kernels that
+// walk a column in one thread use vtrace_step(); the item-parallel kernel
+// computes delta and gain per (t, b) item, runs only step_acc() sequentially
+// and finishes per item -- the same operations in the same order either way.
+__device__ __forceinline__ float step_delta(const Weights& w, float rew, float disc, float val,
+                                            float v_next) {  // vtrace.py:245
+  return __fmul_rn(w.rho_hat, __fsub_rn(__fmaf_rn(disc, v_next, rew), val));
+}
+__device__ __forceinline__ float step_gain(const Weights& w, float disc) {  // gamma_t c_t, :253
+  return __fmul_rn(disc, w.c);
+}
+__device__ __forceinline__ float step_acc(float gain, float acc_next, float delta) {  // :253
+  return __fmaf_rn(gain, acc_next, delta);
+}
+__device__ __forceinline__ float step_pg(const Weights& w, float rew, float disc, float val,
+                                         float vs_next) {  // vtrace.py:275-276
+  return __fmul_rn(w.rho_pg, __fsub_rn(__fmaf_rn(disc, vs_next, rew), val));
+}
+
+// One whole step; updates the carry.
 __device__ __forceinline__ void vtrace_step(const Weights& w, float rew, float disc, float val,
                                             Carry& c, float& vs, float& pg) {
-  const float delta = __fmul_rn(w.rho_hat, __fsub_rn(__fmaf_rn(disc, c.v_next, rew), val));
-  c.acc = __fmaf_rn(__fmul_rn(disc, w.c), c.acc, delta);
-  vs = __fadd_rn(c.acc, val);
-  pg = __fmul_rn(w.rho_pg, __fsub_rn(__fmaf_rn(disc, c.vs_next, rew), val));
+  const float delta = step_delta(w, rew, disc, val, c.v_next);
+  c.acc = step_acc(step_gain(w, disc), c.acc, delta);
+  vs = __fadd_rn(c.acc, val);  // vtrace.py:265
+  pg = step_pg(w, rew, disc, val, c.vs_next);
   c.v_next = val;
   c.vs_next = vs;
 }

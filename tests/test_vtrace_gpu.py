@@ -225,19 +225,41 @@ def test_sm_tile_kernel_matches_oracle(api, T, B, A):
   _check_fused(experiment, inp, path='sm_tile')
 
 
+@pytest.mark.parametrize('T,B,A', [
+    (5, 2, 3), (100, 32, 9), (20, 512, 18), (1, 1, 3), (33, 7, 4), (64, 65, 6),
+    (256, 40, 9), (100, 2048, 9), (50, 130, 18),
+])
+def test_item_kernel_matches_oracle(api, T, B, A):
+  """K2 explicitly: one thread per (t, b) item, T up to 256, compiled-in A."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T * 1000 + B + A)
+  _check_fused(experiment, inp, path='item')
+
+
+def test_item_kernel_limits(api):
+  _, experiment = api
+  with pytest.raises(ValueError, match='item kernel'):
+    _run_fused(experiment, oracle.synthetic_inputs(257, 4, 9, seed=1), path='item')
+  with pytest.raises(ValueError, match='item kernel'):
+    _run_fused(experiment, oracle.synthetic_inputs(5, 4, 5, seed=1), path='item')
+
+
 def test_kernels_agree_bitwise(api):
   """Whatever kernel the heuristics pick, a column gets the same bits."""
   _, experiment = api
   inp = oracle.synthetic_inputs(60, 2048, 18, seed=77)
   outs = {}
-  for path in ('column', 'sm_tile'):
+  for path in ('column', 'sm_tile', 'item'):
     args, out = _run_fused(experiment, inp, path=path)
     out.total_loss.backward()
     outs[path] = (out, args['target_policy_logits'].grad, args['values'].grad)
-  a, b = outs['column'], outs['sm_tile']
-  for f in a[0].vtrace_returns._fields:
-    assert torch.equal(getattr(a[0].vtrace_returns, f), getattr(b[0].vtrace_returns, f)), f
-  assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+  a = outs['column']
+  for other in ('sm_tile', 'item'):
+    b = outs[other]
+    for f in a[0].vtrace_returns._fields:
+      assert torch.equal(getattr(a[0].vtrace_returns, f),
+                         getattr(b[0].vtrace_returns, f)), (other, f)
+    assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]), other
 
 
 def test_sm_tile_refuses_unaligned_batch(api):
