@@ -243,9 +243,10 @@ class FusedCall(object):
     self.launches_per_call = count.value     # kernels of this library per call
     self.plan = text.value.decode().strip()
 
-  def __call__(self):
+  def __call__(self, stream=None):
     rc = self.lib.vtr_from_logits_fused_f32(
-        ctypes.byref(self.p), self.ws.data_ptr(), self.ws_bytes, self.stream)
+        ctypes.byref(self.p), self.ws.data_ptr(), self.ws_bytes,
+        self.stream if stream is None else stream)
     if rc != 0:
       self._lib_mod.check(rc, 'vtr_from_logits_fused_f32')
 
