@@ -58,12 +58,15 @@ def from_logits_fused(
     clip_rho_threshold: float | None, clip_pg_rho_threshold: float | None,
     baseline_cost: float, entropy_cost: float, discounting: float,
     reward_clip_mode: int, want_aux: bool, want_losses: bool,
-    want_grads: bool, path: int
+    want_grads: bool, path: int, pad_grads: bool = False
 ) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor,
            torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
   """Returns (vs, pg_adv, log_rhos, b_lp, t_lp, losses[4], d_logits, d_values).
 
-  Outputs that were not asked for come back as empty tensors.
+  Outputs that were not asked for come back as empty tensors.  With
+  `pad_grads` the two gradient tensors get one extra, zeroed time step at the
+  end ([T+1, ...]): the gradient w.r.t. a learner output of T+1 steps whose
+  last step only feeds the bootstrap value (experiment.py:366-375).
   """
   require_cuda()
   dev = _check_cuda(behaviour_policy_logits, target_policy_logits, actions,
@@ -77,8 +80,12 @@ def from_logits_fused(
   b_lp = torch.empty((T, B), **f32) if want_aux else empty()
   t_lp = torch.empty((T, B), **f32) if want_aux else empty()
   losses = torch.empty(4, **f32) if want_losses else empty()
-  d_logits = torch.empty((T, B, A), **f32) if want_grads else empty()
-  d_values = torch.empty((T, B), **f32) if want_grads else empty()
+  Tg = T + 1 if pad_grads else T
+  d_logits = torch.empty((Tg, B, A), **f32) if want_grads else empty()
+  d_values = torch.empty((Tg, B), **f32) if want_grads else empty()
+  if want_grads and pad_grads:
+    d_logits[T].zero_()
+    d_values[T].zero_()
 
   lib = _lib.load()
   p = _lib.FusedParams()
@@ -123,13 +130,16 @@ def from_logits_fused(
 def _(behaviour_policy_logits, target_policy_logits, actions, discounts,
       rewards, values, bootstrap_value, done, clip_rho_threshold,
       clip_pg_rho_threshold, baseline_cost, entropy_cost, discounting,
-      reward_clip_mode, want_aux, want_losses, want_grads, path):
+      reward_clip_mode, want_aux, want_losses, want_grads, path,
+      pad_grads=False):
   T, B, A = target_policy_logits.shape
   new = target_policy_logits.new_empty
   tb = lambda on: new((T, B)) if on else new((0,))
+  Tg = T + 1 if pad_grads else T
   return (new((T, B)), new((T, B)), tb(want_aux), tb(want_aux), tb(want_aux),
           new((4,)) if want_losses else new((0,)),
-          new((T, B, A)) if want_grads else new((0,)), tb(want_grads))
+          new((Tg, B, A)) if want_grads else new((0,)),
+          new((Tg, B)) if want_grads else new((0,)))
 
 
 # ---------------------------------------------------------------------------
@@ -462,4 +472,51 @@ class FusedLoss(torch.autograd.Function):
       grads[1] = d_logits
     if ctx.needs_input_grad[5]:
       grads[5] = d_values
+    return tuple(grads)
+
+
+class FusedLearnerLoss(torch.autograd.Function):
+  """experiment.py:362-407 on the learner's own [T+1, ...] tensors.
+
+  Takes the learner outputs whole (policy_logits [T+1,B,A], baseline [T+1,B]);
+  the shifts of experiment.py:366-375 are views, and the gradients come back
+  already shaped [T+1, ...] with a zero last step, so autograd never has to
+  pad a [T, ...] gradient into a fresh [T+1, ...] tensor.
+  """
+
+  @staticmethod
+  def forward(ctx, learner_logits, learner_baseline, behaviour_logits, actions,
+              rewards, done, clip_rho_threshold, clip_pg_rho_threshold,
+              baseline_cost, entropy_cost, discounting, reward_clip_mode,
+              want_aux, path):
+    T = learner_logits.shape[0] - 1
+    want_grads = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+    empty = torch.empty(0, dtype=torch.float32, device=learner_logits.device)
+    vs, pg, log_rhos, b_lp, t_lp, losses, d_logits, d_values = from_logits_fused(
+        behaviour_logits[1:], learner_logits[:T], actions[1:], empty,
+        rewards[1:], learner_baseline[:T], learner_baseline[T], done[1:],
+        clip_rho_threshold, clip_pg_rho_threshold, baseline_cost, entropy_cost,
+        discounting, reward_clip_mode, want_aux, True, want_grads, path, True)
+    ctx.save_for_backward(d_logits, d_values)
+    ctx.backward_ran = False
+    total = losses[3].clone()
+    ctx.mark_non_differentiable(vs, pg, log_rhos, b_lp, t_lp, losses)
+    return total, losses, vs, pg, log_rhos, b_lp, t_lp
+
+  @staticmethod
+  @torch.autograd.function.once_differentiable
+  def backward(ctx, g_total, *unused):
+    if ctx.backward_ran:
+      raise RuntimeError('FusedLearnerLoss hands out its stashed gradients in '
+                         'place; backward can run only once per forward')
+    ctx.backward_ran = True
+    d_logits, d_values = ctx.saved_tensors
+    g = _scalar_f32(g_total)
+    scale_inplace(d_logits, g)
+    scale_inplace(d_values, g)
+    grads = [None] * 14
+    if ctx.needs_input_grad[0]:
+      grads[0] = d_logits
+    if ctx.needs_input_grad[1]:
+      grads[1] = d_values
     return tuple(grads)

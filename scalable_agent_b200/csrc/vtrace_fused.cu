@@ -599,7 +599,7 @@ __device__ __forceinline__ unsigned int sm_id() {
 
 // Tile sizing with the speed table (warp 0 of every tile computes the same
 // numbers from the same table): SM s gets granules in proportion to its
-// speed, clamped to [0.8, 1.25] x the even share, plus what is needed for the
+// speed, clamped to [0.7, 1.25] x the even share, plus what is needed for the
 // shares to cover the batch.  Returns this tile's share in granules; falls
 // back to the even share when a share would exceed `cap` granules.
 __device__ __forceinline__ int weighted_share(const SmTileArgs& args, int total_gran, int cap,
@@ -627,7 +627,7 @@ __device__ __forceinline__ int weighted_share(const SmTileArgs& args, int total_
     const int s = lane + 32 * k;
     if (s < nsm) {
       float w = (mean > 0.0f && v[k] > 0.0f) ? v[k] / mean : 1.0f;
-      w = fminf(fmaxf(w, 0.8f), 1.25f);
+      w = fminf(fmaxf(w, 0.7f), 1.25f);
       const int share = static_cast<int>(w * even);
       total += share;
       biggest = max(biggest, share);

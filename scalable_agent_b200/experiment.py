@@ -143,3 +143,74 @@ def compute_vtrace_loss(
       vtrace_returns=vtrace.VTraceFromLogitsReturns(
           vs=vs, pg_advantages=pg, log_rhos=aux[0],
           behaviour_action_log_probs=aux[1], target_action_log_probs=aux[2]))
+
+
+def compute_learner_loss(
+    behaviour_policy_logits, actions, rewards, done,
+    learner_policy_logits, learner_baseline,
+    discounting=.99, reward_clipping='abs_one',
+    baseline_cost=.5, entropy_cost=.00025,
+    clip_rho_threshold=1.0, clip_pg_rho_threshold=1.0,
+    return_aux=False, path='auto'):
+  """The loss block of `build_learner` (`experiment.py:362-407`) on its own inputs.
+
+  Every argument has T+1 time steps, as `build_learner` receives them:
+  `behaviour_policy_logits` / `actions` are the actors' `agent_outputs`,
+  `rewards` / `done` the `env_outputs`, `learner_policy_logits` /
+  `learner_baseline` the result of `agent.unroll`.  This function does what the
+  reference does between the unroll and the optimiser:
+
+    bootstrap_value = learner_baseline[-1]                       # :366
+    agent/env outputs [1:], learner outputs [:-1]                # :372-375
+    clipped_rewards = clip(rewards)                              # :377-382
+    discounts = float(~done) * discounting                       # :384
+    vtrace.from_logits(...) and the three weighted losses        # :389-407
+
+  in one kernel launch: the shifts are views (time is the outermost
+  dimension), clipping and discounts happen inside the kernel, and the
+  gradients w.r.t. `learner_policy_logits` and `learner_baseline` come back in
+  their full [T+1, ...] shape.  Defaults are the reference's flags
+  (`experiment.py:70-74`).
+
+  Returns a `VTraceLossReturns`; only `total_loss` is differentiable.
+  """
+  dev = _device_of(learner_policy_logits, learner_baseline,
+                   behaviour_policy_logits)
+  learner_policy_logits = _to(learner_policy_logits, torch.float32, dev)
+  learner_baseline = _to(learner_baseline, torch.float32, dev)
+  behaviour_policy_logits = _to(behaviour_policy_logits, torch.float32, dev)
+  actions = _to(actions, torch.int32, dev)
+  rewards = _to(rewards, torch.float32, dev)
+  done = _to(done, torch.bool, dev).view(torch.uint8)
+  if reward_clipping not in _lib.REWARD_CLIP_MODES:
+    raise ValueError('unknown reward_clipping %r' % (reward_clipping,))
+  if path not in _lib.PATHS:
+    raise ValueError('unknown path %r' % (path,))
+  _assert_rank(learner_policy_logits, 3, 'learner_policy_logits')
+  _assert_rank(behaviour_policy_logits, 3, 'behaviour_policy_logits')
+  T1, B, A = learner_policy_logits.shape
+  if T1 < 2:
+    raise ValueError('need at least 2 time steps (T+1), got %d' % T1)
+  if tuple(behaviour_policy_logits.shape) != (T1, B, A):
+    raise ValueError('behaviour and learner logits differ in shape')
+  for t, n in ((learner_baseline, 'learner_baseline'), (actions, 'actions'),
+               (rewards, 'rewards'), (done, 'done')):
+    _assert_rank(t, 2, n)
+    if tuple(t.shape) != (T1, B):
+      raise ValueError('%s must have shape [T+1, B] = %s' % (n, (T1, B)))
+
+  total, losses, vs, pg, log_rhos, b_lp, t_lp = _ops.FusedLearnerLoss.apply(
+      learner_policy_logits, learner_baseline, behaviour_policy_logits,
+      actions, rewards, done,
+      _threshold(clip_rho_threshold, 'clip_rho_threshold'),
+      _threshold(clip_pg_rho_threshold, 'clip_pg_rho_threshold'),
+      float(baseline_cost), float(entropy_cost), float(discounting),
+      _lib.REWARD_CLIP_MODES[reward_clipping], bool(return_aux),
+      _lib.PATHS[path])
+  aux = (log_rhos, b_lp, t_lp) if return_aux else (None, None, None)
+  return VTraceLossReturns(
+      total_loss=total, policy_gradient_loss=losses[0],
+      baseline_loss=losses[1], entropy_loss=losses[2],
+      vtrace_returns=vtrace.VTraceFromLogitsReturns(
+          vs=vs, pg_advantages=pg, log_rhos=aux[0],
+          behaviour_action_log_probs=aux[1], target_action_log_probs=aux[2]))

@@ -477,3 +477,40 @@ def test_c_abi_direct_call(api):
   want = [ref.pg_loss, ref.baseline_loss, ref.entropy_loss, ref.total_loss]
   assert_close(_np(losses), want, TOL, 'losses')
   assert_close(_np(losses64), want, TOL, 'losses_f64')
+
+
+@pytest.mark.parametrize('T,B,A,clip', [(20, 48, 9, 'abs_one'),
+                                        (100, 32, 9, 'soft_asymmetric'),
+                                        (7, 130, 18, 'abs_one')])
+def test_learner_loss_on_t_plus_1_tensors(api, T, B, A, clip):
+  """experiment.py:362-407 fed the way build_learner is: [T+1, ...] tensors."""
+  _, experiment = api
+  rng = np.random.default_rng(T + B)
+  learner_logits = rng.standard_normal((T + 1, B, A)).astype(np.float32)
+  behaviour_logits = (learner_logits + 0.5 * rng.standard_normal(
+      (T + 1, B, A))).astype(np.float32)
+  baseline = rng.standard_normal((T + 1, B)).astype(np.float32)
+  actions = rng.integers(0, A, (T + 1, B)).astype(np.int32)
+  rewards = (2 * rng.standard_normal((T + 1, B))).astype(np.float32)
+  done = rng.random((T + 1, B)) < 0.05
+  bc, ec, gamma = 0.5, 0.0033391318945337044, 0.99
+  ref = oracle.fused_vtrace_loss(
+      behaviour_logits[1:], learner_logits[:-1], actions[1:], None,
+      rewards[1:], baseline[:-1], baseline[-1], 1.0, 1.0, bc, ec,
+      reward_clipping=clip, done=done[1:], discounting=gamma)
+  logits_t = _dev(learner_logits).requires_grad_(True)
+  baseline_t = _dev(baseline).requires_grad_(True)
+  out = experiment.compute_learner_loss(
+      _dev(behaviour_logits), _dev(actions), _dev(rewards), _dev(done),
+      logits_t, baseline_t, discounting=gamma, reward_clipping=clip,
+      baseline_cost=bc, entropy_cost=ec, return_aux=True)
+  assert_close(_np(out.vtrace_returns.vs), ref.vs, TOL, 'vs')
+  assert_close(_np(out.vtrace_returns.pg_advantages), ref.pg_advantages, TOL, 'pg')
+  assert_close(_np(out.vtrace_returns.log_rhos), ref.log_rhos, TOL, 'log_rhos')
+  assert_close(_np(out.total_loss), ref.total_loss, TOL, 'total')
+  out.total_loss.backward()
+  assert tuple(logits_t.grad.shape) == (T + 1, B, A)
+  assert_close(_np(logits_t.grad[:-1]), ref.d_target_logits, TOL, 'd_logits')
+  assert_close(_np(baseline_t.grad[:-1]), ref.d_values, TOL, 'd_baseline')
+  assert float(logits_t.grad[-1].abs().max()) == 0.0
+  assert float(baseline_t.grad[-1].abs().max()) == 0.0
