@@ -271,13 +271,35 @@ def run_gpu(args):
   inp = synthetic_on_device(T, B, A, 1000 * rank + 1, device)
   call = FusedCall(inp, T, B, A, device)
   gathered = torch.empty(world, 4, dtype=torch.float32, device=device)
+  # The only cross-GPU traffic of the path: the 4 loss scalars, summed in rank
+  # order (bitwise reproducible).  Preferred: this library's own exchange over
+  # NVLink peer memory; NCCL all-gather if symmetric memory is unavailable.
+  exchange, exchange_kind = None, 'none'
+  if world > 1:
+    exchange_kind = 'nccl all_gather'
+    if args.exchange == 'p2p':
+      try:
+        from scalable_agent_b200.distributed import LossExchange
+        exchange = LossExchange(device)
+        exchange_kind = 'p2p stores over NVLink (vtr_exchange_*), 2 launches'
+      except Exception as e:  # pylint: disable=broad-except
+        exchange_kind = 'nccl all_gather (p2p exchange unavailable: %s)' % (
+            str(e).splitlines()[0][:80])
+    ok = torch.tensor([1 if exchange is not None else 0], device=device)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)   # all ranks must agree
+    if not int(ok.item()):
+      exchange = None
+
+  def exchange_losses():
+    if exchange is not None:
+      return exchange.all_sum(call.out['losses'])
+    dist.all_gather_into_tensor(gathered, call.out['losses'])
+    return gathered
 
   def step():
     call()
     if world > 1:
-      # The only cross-GPU traffic of the path: the loss scalars.  All-gather
-      # then sum in rank order keeps the total bitwise reproducible.
-      dist.all_gather_into_tensor(gathered, call.out['losses'])
+      exchange_losses()
 
   def barrier():
     if world > 1:
@@ -301,7 +323,7 @@ def run_gpu(args):
     call()
     ends[i].record()
     if world > 1:
-      dist.all_gather_into_tensor(gathered, call.out['losses'])
+      exchange_losses()
   t_end.record()
   barrier()
   total_ms = t_begin.elapsed_time(t_end)
@@ -389,8 +411,8 @@ def run_gpu(args):
                         'per GPU, all 5 V-trace fields + d_target_logits + '
                         'd_values + 4 loss scalars written' % (T, B, A),
             'T': T, 'B_per_gpu': B, 'A': A, 'global_B': B * world,
-            'parallelism': 'B sharded over %d rank(s); all-gather of 4 loss '
-                           'scalars per step' % world,
+            'parallelism': 'B sharded over %d rank(s); sum of 4 loss scalars '
+                           'per step via %s' % (world, exchange_kind),
             'l2': 'no flush: %.0f MB of inputs + %.0f MB of outputs per step '
                   'exceed the 126 MB L2' % (
                       (T * B * (8 * A + 16) + 4 * B) / 1e6,
@@ -411,7 +433,8 @@ def run_gpu(args):
                 'ms_per_step': e2e_s / e2e_steps * 1e3,
                 'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + '
                        'backward, pinned host inputs'},
-        'gpu_launches': call.launches_per_call * K,
+        'gpu_launches': (call.launches_per_call +
+                         (2 if exchange is not None else 0)) * K,
         'clocks': dict(sampler.summary(), sampled=clock_note),
     }
   if world > 1:
@@ -442,6 +465,8 @@ def main():
   ap.add_argument('--B', type=int, default=B_DEFAULT, help='columns per GPU')
   ap.add_argument('--A', type=int, default=A_DEFAULT)
   ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--exchange', default='p2p', choices=['p2p', 'nccl'],
+                  help='how the loss scalars are summed over ranks (N > 1)')
   args = ap.parse_args()
   if args.impl == 'reference':
     run_reference(args)

@@ -236,6 +236,29 @@ int vtr_baseline_loss_f32(const float* advantages, int64_t n, float* loss,
 int vtr_baseline_loss_bwd_f32(const float* advantages, const float* grad_out,
                               int64_t n, float* d_advantages, void* stream);
 
+/*
+ * Cross-GPU sum of a few scalars (the loss scalars of a batch sharded over
+ * the GPUs of one box) through NVLink peer memory, without a collective
+ * library call.  No counterpart in the reference, which has a single learner
+ * (experiment.py:491).  Each rank owns a zero-initialised buffer of
+ * vtr_exchange_buffer_bytes(world) bytes that every peer can store to (e.g.
+ * torch symmetric memory); `peer_buffers` is a HOST array of the `world`
+ * device pointers to those buffers as mapped on this rank, its own included.
+ * Per step, with `seq` = 1, 2, 3, ... identical on all ranks:
+ *   vtr_exchange_publish_f32: stores values[0..n) and then seq into slot
+ *     [seq & 1][rank] of every peer's buffer (n <= 6);
+ *   vtr_exchange_collect_f32: waits (at most 2 s, then writes NaN) until all
+ *     `world` slots of parity seq & 1 in this rank's buffer carry seq, and
+ *     writes their sum, accumulated in double in rank order, to sums[0..n).
+ */
+#define VTR_EXCHANGE_MAX_RANKS 16
+#define VTR_EXCHANGE_SLOT_FLOATS 8
+size_t vtr_exchange_buffer_bytes(int32_t world);
+int vtr_exchange_publish_f32(const float* values, int32_t n, void* const* peer_buffers, int32_t rank,
+                             int32_t world, uint32_t seq, void* stream);
+int vtr_exchange_collect_f32(const void* my_buffer, int32_t n, int32_t world, uint32_t seq,
+                             float* sums, void* stream);
+
 /* x[i] *= *scale for i < n, skipped entirely when *scale == 1.  `scale` is a
    device float[1].  Used to apply the upstream gradient of the total loss
    (experiment.py:415) to the gradients the fused pass already produced,

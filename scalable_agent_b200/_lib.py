@@ -90,6 +90,10 @@ SIGNATURES = {
     'vtr_baseline_loss_f32': (ctypes.c_int, [_P, _I64, _P, _P, _SZ, _P]),
     'vtr_baseline_loss_bwd_f32': (ctypes.c_int, [_P, _P, _I64, _P, _P]),
     'vtr_scale_inplace_f32': (ctypes.c_int, [_P, _P, _I64, _P]),
+    'vtr_exchange_buffer_bytes': (_SZ, [_I32]),
+    'vtr_exchange_publish_f32':
+        (ctypes.c_int, [_P, _I32, ctypes.POINTER(ctypes.c_void_p), _I32, _I32, _U32, _P]),
+    'vtr_exchange_collect_f32': (ctypes.c_int, [_P, _I32, _I32, _U32, _P, _P]),
 }
 
 _lib = None

@@ -8,6 +8,8 @@ only exchange is the loss scalars: they are all-gathered and summed in rank
 order, so the global loss is bitwise reproducible whatever algorithm NCCL
 picks.  Gradients w.r.t. logits and values are per-sample and stay local.
 """
+import ctypes
+
 import torch
 import torch.distributed as dist
 
@@ -65,3 +67,60 @@ def compute_vtrace_loss_sharded(*args, group=None, **kwargs):
   local = torch.stack([out.total_loss.detach(), out.policy_gradient_loss,
                        out.baseline_loss, out.entropy_loss])
   return out, all_reduce_losses(local, group=group)
+
+
+class LossExchange(object):
+  """Sum of the loss scalars over the ranks of one box through NVLink peer memory.
+
+  Every rank stores its values straight into every peer's buffer (torch
+  symmetric memory, P2P stores over NVLink / NVSwitch) and sums what has
+  arrived in rank order: two tiny kernels of this library per step
+  (`vtr_exchange_publish_f32`, `vtr_exchange_collect_f32`) instead of a
+  collective library call, and identical bits on every rank.  Construct once
+  (collective: every rank must), then call `all_sum` once per step on every
+  rank, in the same order.
+  """
+
+  def __init__(self, device, group=None, max_values=4):
+    from scalable_agent_b200 import _lib
+    import torch.distributed._symmetric_memory as symm_mem
+    self._lib = _lib
+    self.lib = _lib.load()
+    self.group = group if group is not None else dist.group.WORLD
+    self.world = dist.get_world_size(self.group)
+    self.rank = dist.get_rank(self.group)
+    self.device = torch.device(device)
+    if not 1 <= max_values <= 6:
+      raise ValueError('max_values must be in 1..6')
+    if self.world > 16:
+      raise ValueError('LossExchange supports up to 16 ranks')
+    nbytes = self.lib.vtr_exchange_buffer_bytes(self.world)
+    self.buffer = symm_mem.empty(nbytes // 4, dtype=torch.float32,
+                                 device=self.device)
+    self.buffer.zero_()
+    self.handle = symm_mem.rendezvous(self.buffer, self.group)
+    ptrs = list(self.handle.buffer_ptrs)
+    self._peer_ptrs = (ctypes.c_void_p * self.world)(*ptrs)
+    self.seq = 0
+    torch.cuda.synchronize(self.device)
+    dist.barrier(self.group)   # every buffer is zeroed before anyone publishes
+
+  def all_sum(self, values):
+    """values: float32 tensor [n], n <= 6, on this rank's device -> sum over ranks."""
+    flat = values.detach().reshape(-1)
+    if flat.dtype != torch.float32 or not flat.is_contiguous():
+      flat = flat.to(torch.float32).contiguous()
+    n = flat.numel()
+    out = torch.empty(n, dtype=torch.float32, device=self.device)
+    self.seq += 1
+    stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+    with torch.cuda.device(self.device):
+      rc = self.lib.vtr_exchange_publish_f32(
+          flat.data_ptr(), n, self._peer_ptrs, self.rank, self.world, self.seq,
+          stream)
+      self._lib.check(rc, 'vtr_exchange_publish_f32')
+      rc = self.lib.vtr_exchange_collect_f32(
+          self.buffer.data_ptr(), n, self.world, self.seq, out.data_ptr(),
+          stream)
+      self._lib.check(rc, 'vtr_exchange_collect_f32')
+    return out.reshape(values.shape)
