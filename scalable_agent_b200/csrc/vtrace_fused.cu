@@ -1,1085 +1,39 @@
-// Fused V-trace + IMPALA loss, forward and backward, one pass over HBM.
+// Fused V-trace + IMPALA loss, forward and backward, one pass over HBM:
+// kernel selection, launch and the C entry points.
 //
 // Replaces vtrace.from_logits (vtrace.py:71-161), the three loss helpers
 // (experiment.py:324-343), the weighted total (experiment.py:401-407) and the
 // autodiff backward of that total (experiment.py:415).
 //
-// K1 (this file).  A tile is 32 adjacent batch columns, one lane per column,
-// walked from t = T-1 down to 0 so that the reverse recurrence
-// acc_t = delta_t + gamma_t c_t acc_{t+1} (vtrace.py:250-262) and vs_{t+1}
-// (vtrace.py:268-269) are carried, not recomputed.  For one time step the 32
-// columns' logits are ONE contiguous run of 32*A floats in the time-major
-// [T,B,A] layout; a ring of `depth` slots in shared memory is kept full by TMA
-// bulk copies (cp.async.bulk -> mbarrier complete_tx) for both logits tensors
-// plus 4-byte cp.async for the four [T,B] operands, all landing on the slot's
-// one mbarrier.  d_target_logits rows are staged in shared memory and leave
-// with TMA bulk stores.  Two shells run the same arithmetic (vtrace_math.cuh):
-//   K1a fused_column_kernel  one warp per tile, deepest ring   (>= 7 tiles/SM)
-//   K1b fused_relay_kernel   W warps per tile relaying the carry (< 7 tiles/SM)
-// Losses accumulate per lane in double, are reduced with a fixed shuffle tree
-// and written as one partial per tile; K3 (reduce_losses_kernel) sums the
-// partials in a fixed order.  No atomics.
+// A lane owns a batch column and time is walked from t = T-1 down to 0, so the
+// reverse recurrence acc_t = delta_t + gamma_t c_t acc_{t+1} (vtrace.py:250-262)
+// and vs_{t+1} (vtrace.py:268-269) are carried, not recomputed.  For one time
+// step the logits of adjacent columns are ONE contiguous run in the time-major
+// [T,B,A] layout; rings of shared-memory slots are kept full by TMA bulk copies
+// (cp.async.bulk -> mbarrier complete_tx), gradient rows leave with TMA bulk
+// stores.  All kernels take their arithmetic from vtrace_math.cuh:
+//   K1a fused_column_kernel   fused_column.cuh   32-column tile, one warp
+//   K1b fused_relay_kernel    fused_relay.cuh    32-column tile, W warps relaying the carry
+//   K1c fused_sm_tile_kernel  fused_sm_tile.cuh  one wide tile per SM, producer/consumer ring,
+//                                                speed-weighted tiles, in-kernel final reduction
+//   K2  fused_item_kernel     fused_item.cuh     one thread per (t, b) item, tiny batches
+//   K3  reduce_losses_kernel  (below)            second stage of the loss reduction
+// Losses accumulate per lane in double and are reduced in fixed orders; the
+// only atomics are two tickets in K1c (which tile next, who finished last).
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include "common.h"
+#include "fused_column.cuh"
+#include "fused_common.cuh"
+#include "fused_item.cuh"
+#include "fused_relay.cuh"
+#include "fused_sm_tile.cuh"
 #include "ptx.cuh"
 #include "vtrace_math.cuh"
 
 namespace vtr {
-
-struct FusedArgs {
-  int T, B, A;
-  int depth;        // ring slots
-  int slot_floats;  // floats per ring slot: 2*32*A logits + 4*32 per-step operands
-  uint32_t flags;
-  int reward_clip_mode;
-  int tma_in_ok;   // logits rows are 16-byte aligned for every t and tile
-  int tma_out_ok;  // same for d_target_logits
-  float clip_rho, clip_pg_rho, baseline_cost, entropy_cost, discounting;
-  const float* blog;
-  const float* tlog;
-  const int32_t* actions;
-  const float* discounts;
-  const float* rewards;
-  const float* values;
-  const float* bootstrap;
-  const uint8_t* done;
-  float* vs;
-  float* pg;
-  float* log_rhos;
-  float* b_lp;
-  float* t_lp;
-  float* d_logits;
-  float* d_values;
-  double* partials;  // loss partials, or null
-  float* losses;       // K1c only: final losses written by the last tile to finish
-  double* losses_f64;  // K1c only
-};
-
-constexpr int kColumnsPerTile = 32;
-constexpr int kColumnBarrierBytes = 128;  // K1a: up to 16 "slot full" mbarriers
-constexpr int kRelayBarrierBytes = 256;   // K1b: 16 "slot full" + 16 "carry arrived"
-constexpr int kMaxDepth = 16;
-constexpr int kMaxWarps = 16;
-
-template <int N>
-__device__ __forceinline__ void load_row(float (&x)[N], const float* row) {
-  if constexpr (N % 4 == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 4; ++i) {
-      float4 v = reinterpret_cast<const float4*>(row)[i];
-      x[4 * i] = v.x, x[4 * i + 1] = v.y, x[4 * i + 2] = v.z, x[4 * i + 3] = v.w;
-    }
-  } else if constexpr (N % 2 == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 2; ++i) {
-      float2 v = reinterpret_cast<const float2*>(row)[i];
-      x[2 * i] = v.x, x[2 * i + 1] = v.y;
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < N; ++i) x[i] = row[i];
-  }
-}
-
-template <int N>
-__device__ __forceinline__ void store_row(float* row, const float (&x)[N]) {
-  if constexpr (N % 4 == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 4; ++i)
-      reinterpret_cast<float4*>(row)[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
-  } else if constexpr (N % 2 == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 2; ++i) reinterpret_cast<float2*>(row)[i] = make_float2(x[2 * i], x[2 * i + 1]);
-  } else {
-#pragma unroll
-    for (int i = 0; i < N; ++i) row[i] = x[i];
-  }
-}
-
-__device__ __forceinline__ double warp_sum_fixed(double v) {
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-  return v;
-}
-
-// Fills ring slot `s` (shared address `dst`, mbarrier `bar`) with time step `t`
-// of the tile starting at column b0.  Called by all 32 lanes of one warp; the
-// barrier expects 33 arrivals: every lane's cp.async group + lane 0's arm.
-__device__ __forceinline__ void issue_step(const FusedArgs& a, int t, uint32_t dst, uint32_t bar,
-                                           int lane, int b0, int nb, int A, bool tma_in,
-                                           uint64_t policy) {
-  const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
-  const size_t row0 = (static_cast<size_t>(t) * a.B + b0) * A;
-  if (tma_in) {
-    if (lane == 0) {
-      ptx::mbar_arrive_expect_tx(bar, 2u * row_bytes);
-      ptx::bulk_g2s(dst, a.blog + row0, row_bytes, bar, policy);
-      ptx::bulk_g2s(dst + 32u * A * 4u, a.tlog + row0, row_bytes, bar, policy);
-    }
-  } else {
-    if (lane == 0) ptx::mbar_arrive(bar);
-    for (int i = lane; i < nb * A; i += 32) {
-      ptx::cp_async4(dst + 4u * i, a.blog + row0 + i);
-      ptx::cp_async4(dst + (32u * A + i) * 4u, a.tlog + row0 + i);
-    }
-  }
-  if (lane < nb) {
-    const size_t e = static_cast<size_t>(t) * a.B + b0 + lane;
-    const uint32_t sc = dst + (64u * A + lane) * 4u;
-    ptx::cp_async4(sc, a.actions + e);
-    if (a.discounts) ptx::cp_async4(sc + 128u, a.discounts + e);
-    ptx::cp_async4(sc + 256u, a.rewards + e);
-    ptx::cp_async4(sc + 384u, a.values + e);
-  }
-  ptx::cp_async_mbar_arrive_noinc(bar);
-}
-
-// ---------------------------------------------------------------------------
-// K1a: one warp per tile.  Used when an SM has to hold so many tiles (>= 7)
-// that shared memory allows only one warp's worth of ring per tile: the whole
-// ring (5 slots at A=18) then runs ahead of the single consumer.
-// ---------------------------------------------------------------------------
-template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant__ FusedArgs a) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int A = A_CT > 0 ? A_CT : a.A;
-  const int T = a.T, B = a.B;
-  const int lane = threadIdx.x;
-  const int b0 = blockIdx.x * kColumnsPerTile;
-  const int nb = min(kColumnsPerTile, B - b0);
-  const bool active = lane < nb;
-  const int b = b0 + (active ? lane : 0);
-  const int depth = a.depth;
-  const int slot_floats = a.slot_floats;
-
-  float* ring = reinterpret_cast<float*>(smem_raw + kColumnBarrierBytes);
-  float* outbuf = ring + static_cast<size_t>(depth) * slot_floats;  // 2 x [32*A], GRADS only
-  const uint32_t bars = ptx::smem_u32(smem_raw);
-  const uint32_t ring_u32 = ptx::smem_u32(ring);
-  const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
-  const int row_elems = nb * A;
-  const bool tma_in = a.tma_in_ok && (row_bytes % 16u == 0);
-  const bool tma_out = a.tma_out_ok && (row_bytes % 16u == 0);
-  const bool need_softmax = GRADS || a.partials != nullptr;
-
-  if (lane == 0) {
-    for (int s = 0; s < depth; ++s) ptx::mbar_init(bars + 8u * s, 33);
-    ptx::fence_mbar_init();
-    ptx::fence_proxy_async();
-  }
-  __syncwarp();
-  const uint64_t policy = ptx::policy_evict_first();
-
-  auto issue = [&](int t, int s) {
-    issue_step(a, t, ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u, bars + 8u * s, lane, b0,
-               nb, A, tma_in, policy);
-  };
-  const int prologue = min(depth, T);
-  for (int k = 0; k < prologue; ++k) issue(T - 1 - k, k);
-
-  math::Carry carry;
-  carry.acc = 0.0f;
-  carry.v_next = active ? a.bootstrap[b] : 0.0f;
-  carry.vs_next = carry.v_next;
-  math::LossSums sums = {0.0, 0.0, 0.0};
-  uint8_t done_next = 0;
-  if (a.done && active) done_next = a.done[static_cast<size_t>(T - 1) * B + b];
-
-  int s = 0;
-  uint32_t parity = 0;
-  for (int it = 0; it < T; ++it) {
-    const int t = T - 1 - it;
-    const size_t e = static_cast<size_t>(t) * B + b;
-    const uint8_t done_cur = done_next;
-    if (a.done && active && t > 0) done_next = a.done[e - B];
-
-    if (GRADS) {
-      // The staging buffer written this step was handed to a bulk store two
-      // steps ago; wait until that store has finished reading it.
-      if (tma_out && lane == 0) ptx::bulk_wait_read<1>();
-      __syncwarp();
-    }
-    ptx::mbar_wait(bars + 8u * s, parity);
-
-    const float* slot = ring + static_cast<size_t>(s) * slot_floats;
-    const float* xb_row = slot + lane * A;
-    const float* xt_row = slot + 32 * A + lane * A;
-    const float* sc = slot + 64 * A;
-    float* orow = outbuf + (it & 1) * 32 * A + lane * A;
-
-    // ---- operands and rows out of the slot ----
-    int act = 0;
-    float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
-    math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
-    float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
-    if (active) {
-      act = __float_as_int(sc[lane]);
-      act = min(max(act, 0), A - 1);
-      disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
-      rew = sc[64 + lane];
-      val = sc[96 + lane];
-      xa_t = xt_row[act];
-      xa_b = xb_row[act];
-      if constexpr (A_CT > 0) {
-        float xb[A_CT];
-        load_row(xb, xb_row);
-        sb = math::row_stats(xb);
-        load_row(x, xt_row);
-      }
-    }
-    if constexpr (A_CT > 0) {
-      // The rows are in registers: the slot can take step it+depth already.
-      __syncwarp();
-      if (it + depth < T) issue(t - depth, s);
-    }
-
-    if (active) {
-      rew = math::clip_reward(rew, a.reward_clip_mode);
-      // ---- action log-probs of both policies (vtrace.py:143-146) ----
-      if constexpr (A_CT > 0) {
-        st = math::row_stats(x, ex);
-      } else {
-        st = math::smem_row_stats(xt_row, A);
-        sb = math::smem_row_stats(xb_row, A);
-      }
-      const float t_lp = math::action_log_prob(xa_t, st);
-      const float b_lp = math::action_log_prob(xa_b, sb);
-      const float log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
-
-      // ---- V-trace step (vtrace.py:235-276), walking t downwards ----
-      const math::Weights w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
-      float vs, pg;
-      math::vtrace_step(w, rew, disc, val, carry, vs, pg);
-
-      if (a.vs) a.vs[e] = vs;
-      if (a.pg) a.pg[e] = pg;
-      if (a.log_rhos) a.log_rhos[e] = log_rho;
-      if (a.b_lp) a.b_lp[e] = b_lp;
-      if (a.t_lp) a.t_lp[e] = t_lp;
-
-      // ---- losses (experiment.py:324-343) and their gradients ----
-      if (need_softmax) {
-        const float inv_sum = __frcp_rn(st.sum);
-        float entropy;
-        if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
-        else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
-        if (GRADS) {
-          // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
-          const float ka = __fmul_rn(a.entropy_cost, inv_sum);
-          const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
-          if constexpr (A_CT > 0) {
-            math::row_gradient(ex, x, ka, kb);
-            store_row(orow, ex);
-          } else {
-            math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
-          }
-          orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
-          if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
-        }
-        if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
-      }
-    }
-
-    if (GRADS) {
-      float* gdst = a.d_logits + (static_cast<size_t>(t) * B + b0) * A;
-      if (tma_out) {
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          ptx::bulk_s2g(gdst, ptx::smem_u32(outbuf + (it & 1) * 32 * A), row_bytes);
-          ptx::bulk_commit();
-        }
-      } else {
-        __syncwarp();
-        const float* src = outbuf + (it & 1) * 32 * A;
-        for (int i = lane; i < row_elems; i += 32) gdst[i] = src[i];
-      }
-    }
-    if constexpr (A_CT == 0) {
-      // run-time A re-reads the rows from the slot: refill only now
-      __syncwarp();
-      if (it + depth < T) issue(t - depth, s);
-    }
-    if (++s == depth) s = 0, parity ^= 1u;
-  }
-
-  if (a.partials) {
-    const double pg_sum = warp_sum_fixed(sums.pg);
-    const double bl_sum = warp_sum_fixed(sums.baseline);
-    const double ent_sum = warp_sum_fixed(sums.entropy);
-    if (lane == 0) {
-      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
-      out[0] = pg_sum, out[1] = bl_sum, out[2] = ent_sum;
-    }
-  }
-  if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
-}
-
-// ---------------------------------------------------------------------------
-// K1b: several warps per tile, passing the recurrence along ("relay").  Warp w
-// owns the time steps it = w, w+W, ... (it counts from the end: t = T-1-it);
-// each does its whole step in its own registers and only the 3-float carry
-// (acc, V_{t+1}, vs_{t+1}) per lane travels from the owner of step t+1 to the
-// owner of step t, through shared memory and an mbarrier.  Everything that
-// does not depend on the carry (both softmaxes, log_rho, rho, the entropy:
-// most of the work) overlaps between warps, so a tile advances much faster
-// than one warp can; used whenever shared memory leaves room for it.
-//
-// Shared memory of one tile, in bytes from the start:
-//   [0,128)    `depth` mbarriers "slot full"      (TMA + cp.async completion)
-//   [128,256)  `warps` mbarriers "carry arrived"  (recurrence hand-off)
-//   ring       depth slots of slot_floats floats: one time step of the tile each
-//   staging    warps x 32*A floats: each warp's d_target_logits row  (GRADS only)
-//   carry      warps x 3 x 32 floats: (acc, V_{t+1}, vs_{t+1}) per lane
-//   sums       warps x 3 doubles: per-warp loss partials
-//
-// Launch bound 768 threads (never more than 512 are launched) caps the kernel
-// at 80 registers, so that 24 warps fit an SM's register file.
-// ---------------------------------------------------------------------------
-template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ FusedArgs a) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int A = A_CT > 0 ? A_CT : a.A;
-  const int T = a.T, B = a.B;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int W = blockDim.x >> 5;
-  const int b0 = blockIdx.x * kColumnsPerTile;
-  const int nb = min(kColumnsPerTile, B - b0);
-  const bool active = lane < nb;
-  const int b = b0 + (active ? lane : 0);
-  const int depth = a.depth;
-  const int slot_floats = a.slot_floats;
-
-  float* ring = reinterpret_cast<float*>(smem_raw + kRelayBarrierBytes);
-  float* staging = ring + static_cast<size_t>(depth) * slot_floats;
-  float* carry_buf = staging + (GRADS ? W * 32 * A : 0);
-  double* warp_sums = reinterpret_cast<double*>(carry_buf + W * 96);
-  const uint32_t full_bars = ptx::smem_u32(smem_raw);
-  const uint32_t carry_bars = full_bars + 128u;
-  const uint32_t ring_u32 = ptx::smem_u32(ring);
-  const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
-  const int row_elems = nb * A;
-  const bool tma_in = a.tma_in_ok && (row_bytes % 16u == 0);
-  const bool tma_out = a.tma_out_ok && (row_bytes % 16u == 0);
-  const bool need_softmax = GRADS || a.partials != nullptr;
-  float* orow_base = staging + warp * 32 * A;  // this warp's gradient row
-  float* orow = orow_base + lane * A;
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < depth; ++s) ptx::mbar_init(full_bars + 8u * s, 33);
-    for (int w = 0; w < W; ++w) ptx::mbar_init(carry_bars + 8u * w, 32);
-    ptx::fence_mbar_init();
-    ptx::fence_proxy_async();
-  }
-  __syncthreads();
-  const uint64_t policy = ptx::policy_evict_first();
-
-  auto issue = [&](int t, int s) {
-    issue_step(a, t, ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u, full_bars + 8u * s, lane,
-               b0, nb, A, tma_in, policy);
-  };
-  // Step `it` lives in ring slot it % depth and is loaded by the warp that owns it.
-  for (int it = warp; it < min(depth, T); it += W) issue(T - 1 - it, it);
-
-  math::LossSums sums = {0.0, 0.0, 0.0};
-
-  for (int it = warp; it < T; it += W) {
-    const int t = T - 1 - it;
-    const size_t e = static_cast<size_t>(t) * B + b;
-    const int s = it % depth;
-    const uint8_t done_cur = (a.done && active) ? a.done[e] : 0;
-
-    ptx::mbar_wait(full_bars + 8u * s, (it / depth) & 1);
-    const float* slot = ring + static_cast<size_t>(s) * slot_floats;
-    const float* xb_row = slot + lane * A;
-    const float* xt_row = slot + 32 * A + lane * A;
-    const float* sc = slot + 64 * A;
-
-    // ---- phase A: everything that does not depend on step t+1 ----
-    int act = 0;
-    float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
-    math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
-    float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
-    if (active) {
-      act = __float_as_int(sc[lane]);
-      act = min(max(act, 0), A - 1);
-      disc = a.done ? (done_cur ? 0.0f : a.discounting) : sc[32 + lane];
-      rew = sc[64 + lane];
-      val = sc[96 + lane];
-      xa_t = xt_row[act];
-      xa_b = xb_row[act];
-      if constexpr (A_CT > 0) {
-        // behaviour row first: it reduces to its statistics and frees its registers
-        float xb[A_CT];
-        load_row(xb, xb_row);
-        sb = math::row_stats(xb);
-        load_row(x, xt_row);
-      }
-    }
-    if constexpr (A_CT > 0) {
-      // The rows are in registers: the slot can take step it+depth already.
-      __syncwarp();
-      if (it + depth < T) issue(t - depth, s);
-    }
-    float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
-    float entropy = 0.0f, inv_sum = 0.0f;
-    math::Weights w = {0.0f, 0.0f, 0.0f};
-    if (active) {
-      rew = math::clip_reward(rew, a.reward_clip_mode);
-      // action log-probs of both policies (vtrace.py:143-146)
-      if constexpr (A_CT > 0) {
-        st = math::row_stats(x, ex);
-      } else {
-        st = math::smem_row_stats(xt_row, A);
-        sb = math::smem_row_stats(xb_row, A);
-      }
-      t_lp = math::action_log_prob(xa_t, st);
-      b_lp = math::action_log_prob(xa_b, sb);
-      log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
-      w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
-      if (need_softmax) {
-        inv_sum = __frcp_rn(st.sum);
-        if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
-        else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
-      }
-    }
-
-    // ---- phase B: the V-trace step (vtrace.py:243-276); needs step t+1 ----
-    math::Carry carry;
-    if (it == 0) {
-      carry.acc = 0.0f;
-      carry.v_next = active ? a.bootstrap[b] : 0.0f;
-      carry.vs_next = carry.v_next;
-    } else {
-      // n-th use of this warp's carry slot: steps warp, warp+W, ... (step 0 has none)
-      const int use = it / W - (warp == 0 ? 1 : 0);
-      ptx::mbar_wait(carry_bars + 8u * warp, use & 1);
-      const float* cb = carry_buf + warp * 96;
-      carry.acc = cb[lane], carry.v_next = cb[32 + lane], carry.vs_next = cb[64 + lane];
-    }
-    float vs, pg;
-    math::vtrace_step(w, rew, disc, val, carry, vs, pg);
-    if (it + 1 < T) {
-      const int nw = warp + 1 == W ? 0 : warp + 1;  // owner of step it+1
-      float* cb = carry_buf + nw * 96;
-      cb[lane] = carry.acc, cb[32 + lane] = carry.v_next, cb[64 + lane] = carry.vs_next;
-      ptx::mbar_arrive(carry_bars + 8u * nw);
-    }
-
-    // ---- phase C: outputs, gradient row, loss terms ----
-    if (GRADS) {
-      // this warp's previous bulk store must have read the staging row
-      if (tma_out && lane == 0) ptx::bulk_wait_read<0>();
-      __syncwarp();
-    }
-    if (active) {
-      if (a.vs) a.vs[e] = vs;
-      if (a.pg) a.pg[e] = pg;
-      if (a.log_rhos) a.log_rhos[e] = log_rho;
-      if (a.b_lp) a.b_lp[e] = b_lp;
-      if (a.t_lp) a.t_lp[e] = t_lp;
-      if (GRADS) {
-        // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
-        const float ka = __fmul_rn(a.entropy_cost, inv_sum);
-        const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
-        if constexpr (A_CT > 0) {
-          math::row_gradient(ex, x, ka, kb);
-          store_row(orow, ex);
-        } else {
-          math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
-        }
-        orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
-        if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
-      }
-      if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
-    }
-    if (GRADS) {
-      float* gdst = a.d_logits + (static_cast<size_t>(t) * B + b0) * A;
-      if (tma_out) {
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          ptx::bulk_s2g(gdst, ptx::smem_u32(orow_base), row_bytes);
-          ptx::bulk_commit();
-        }
-      } else {
-        __syncwarp();
-        for (int i = lane; i < row_elems; i += 32) gdst[i] = orow_base[i];
-        __syncwarp();
-      }
-    }
-    if constexpr (A_CT == 0) {
-      // run-time A re-reads the rows from the slot: refill only now
-      __syncwarp();
-      if (it + depth < T) issue(t - depth, s);
-    }
-  }
-
-  if (a.partials) {
-    const double pg_sum = warp_sum_fixed(sums.pg);
-    const double bl_sum = warp_sum_fixed(sums.baseline);
-    const double ent_sum = warp_sum_fixed(sums.entropy);
-    if (lane == 0)
-      warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int w = 0; w < W; ++w)
-        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
-      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
-      out[0] = p0, out[1] = p1, out[2] = p2;
-    }
-  }
-  if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
-}
-
-// ---------------------------------------------------------------------------
-// K1c: one persistent tile per SM ("SM tile").  The batch is split into
-// G (a multiple of the SM count) contiguous column ranges of equal width, up
-// to 256 columns each, so every SM streams the same number of bytes.  All
-// column groups of a tile share ONE ring: a producer warp fills slot after slot
-// with six TMA bulk copies per time step (two logits rows of ncols*A floats,
-// four operand rows of ncols floats: runs of up to 18 KB, which keeps DRAM
-// pages open), consumer warps wait on the slot's "full" mbarrier, pull their
-// rows into registers and hand the slot back through its "empty" mbarrier
-// straight away, long before their arithmetic is done.  Consumer warp
-// (g, r) owns columns [32g, 32g+32) of the tile and the time steps
-// it = r, r+R, ...; the R warps of a column group relay the recurrence carry
-// as in K1b (R = 1: the carry stays in registers).  Needs 16-byte aligned
-// rows: B % 4 == 0 and 16-byte aligned base pointers; anything else goes to
-// K1a/K1b.
-//
-// Shared memory of one tile, in bytes from the start:
-//   [0,128)    depth mbarriers "slot full"   (count 1 + tx bytes)
-//   [128,256)  depth mbarriers "slot empty"  (count = column groups)
-//   [256,384)  groups*relay mbarriers "carry arrived" (count 32)
-//   ring       depth slots: blog[cols*A] tlog[cols*A] actions[cols] discounts[cols]
-//              rewards[cols] values[cols], cols = 32*groups
-//   staging    per consumer warp, staging_bufs x 32*A floats   (GRADS only)
-//   carry      per consumer warp 3 x 32 floats
-//   sums       per consumer warp 3 doubles
-// ---------------------------------------------------------------------------
-constexpr int kSmBarrierBytes = 512;
-constexpr int kSmMaxConsumerWarps = 18;
-constexpr int kMaxSms = 256;
-
-// Measured streaming speed of every SM (columns x steps per ns, smoothed over
-// calls), written by K1c at the end of each tile and read at the start of the
-// next call to size the tiles.  SMs do not get equal shares of the memory
-// system (on B200 the spread between the fastest and the slowest SM under full
-// load is ~40 %, fixed by where the SM sits), so equal tiles leave the fast SMs
-// idle for the last quarter of the kernel.  Only the partition depends on
-// this table; every output value is independent of the partition.
-static __device__ float g_sm_speed[kMaxSms];
-
-struct SmTileArgs {
-  FusedArgs f;
-  int groups;        // column groups (warps side by side) per tile = capacity / 32
-  int relay;         // warps per column group, owning interleaved time steps
-  int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
-  int num_sm;        // SMs of the device
-  int waves;         // tiles per SM (grid = num_sm * waves) when balancing
-  unsigned int* cursor;  // zeroed column cursor for speed-weighted tiles, or null
-};
-
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __forceinline__ unsigned int sm_id() {
-  unsigned int s;
-  asm volatile("mov.u32 %0, %%smid;" : "=r"(s));
-  return s;
-}
-
-// Tile sizing with the speed table (warp 0 of every tile computes the same
-// numbers from the same table): SM s gets granules in proportion to its
-// speed, clamped to [0.7, 1.25] x the even share, plus what is needed for the
-// shares to cover the batch.  Returns this tile's share in granules; falls
-// back to the even share when a share would exceed `cap` granules.
-__device__ __forceinline__ int weighted_share(const SmTileArgs& args, int total_gran, int cap,
-                                              int lane, unsigned int my_sm) {
-  const int nsm = args.num_sm, grid = nsm * args.waves;
-  float v[kMaxSms / 32];
-  float sum = 0.0f;
-  int cnt = 0;
-#pragma unroll
-  for (int k = 0; k < kMaxSms / 32; ++k) {
-    const int s = lane + 32 * k;
-    v[k] = s < nsm ? g_sm_speed[s] : 0.0f;
-    if (v[k] > 0.0f) sum += v[k], ++cnt;
-  }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    sum += __shfl_xor_sync(0xffffffffu, sum, off);
-    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
-  }
-  const float mean = cnt > 0 ? sum / cnt : 0.0f;
-  const float even = static_cast<float>(total_gran) / grid;
-  int total = 0, biggest = 0, mine = 0;
-#pragma unroll
-  for (int k = 0; k < kMaxSms / 32; ++k) {
-    const int s = lane + 32 * k;
-    if (s < nsm) {
-      float w = (mean > 0.0f && v[k] > 0.0f) ? v[k] / mean : 1.0f;
-      w = fminf(fmaxf(w, 0.7f), 1.25f);
-      const int share = static_cast<int>(w * even);
-      total += share;
-      biggest = max(biggest, share);
-      if (s == static_cast<int>(my_sm)) mine = share;
-    }
-  }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    total += __shfl_xor_sync(0xffffffffu, total, off);
-    biggest = max(biggest, __shfl_xor_sync(0xffffffffu, biggest, off));
-    mine = max(mine, __shfl_xor_sync(0xffffffffu, mine, off));
-  }
-  // Shares were rounded down: hand the missing granules out evenly, the
-  // remainder to the lowest SM ids, so that the shares add up to the batch.
-  const int deficit = max(0, total_gran - total * args.waves);
-  const int add = deficit / grid, rem = deficit - add * grid;
-  const int bump_below = (rem + args.waves - 1) / args.waves;
-  if (biggest + add + 1 > cap || my_sm >= static_cast<unsigned int>(nsm))
-    return min(cap, (total_gran + grid - 1) / grid);
-  return mine + add + (static_cast<int>(my_sm) < bump_below ? 1 : 0);
-}
-
-template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
-    fused_sm_tile_kernel(const __grid_constant__ SmTileArgs args) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  const FusedArgs& a = args.f;
-  const int A = A_CT > 0 ? A_CT : a.A;
-  const int T = a.T, B = a.B;
-  const int NG = args.groups, R = args.relay, depth = a.depth;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int consumers = NG * R;
-  const int cols = 32 * NG;  // slot stride in columns
-
-  // This tile's column range, in granules of 4 columns (16-byte rows).  With a
-  // cursor: speed-weighted shares handed out first come, first served.
-  // Without: B/4 granules dealt evenly by block index.
-  __shared__ int sh_range[2];
-  const int total_gran = B >> 2;
-  const unsigned long long t_begin = global_timer_ns();
-  if (args.cursor) {
-    if (warp == 0) {
-      const int share = weighted_share(args, total_gran, cols >> 2, lane, sm_id());
-      if (lane == 0) {
-        const unsigned int start = atomicAdd(args.cursor, static_cast<unsigned int>(share * 4));
-        sh_range[0] = static_cast<int>(min(start, static_cast<unsigned int>(B)));
-        sh_range[1] = max(0, min(share * 4, B - sh_range[0]));
-      }
-    }
-  } else if (threadIdx.x == 0) {
-    const int G = gridDim.x, c = blockIdx.x;
-    const int base = total_gran / G, rem = total_gran % G;
-    sh_range[0] = (c * base + min(c, rem)) * 4;
-    sh_range[1] = (base + (c < rem ? 1 : 0)) * 4;
-  }
-
-  const int slot_floats = cols * (2 * A + 4);
-  float* ring = reinterpret_cast<float*>(smem_raw + kSmBarrierBytes);
-  float* staging = ring + static_cast<size_t>(depth) * slot_floats;
-  float* carry_buf = staging + (GRADS ? consumers * args.staging_bufs * 32 * A : 0);
-  double* lane_sums = reinterpret_cast<double*>(carry_buf + consumers * 96);  // [consumer][k][lane]
-  const uint32_t full_bars = ptx::smem_u32(smem_raw);
-  const uint32_t empty_bars = full_bars + 128u;
-  const uint32_t carry_bars = full_bars + 256u;
-  const uint32_t ring_u32 = ptx::smem_u32(ring);
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < depth; ++s) {
-      ptx::mbar_init(full_bars + 8u * s, 1);
-      ptx::mbar_init(empty_bars + 8u * s, NG);
-    }
-    for (int w = 0; w < consumers; ++w) ptx::mbar_init(carry_bars + 8u * w, 32);
-    ptx::fence_mbar_init();
-    ptx::fence_proxy_async();
-  }
-  __syncthreads();
-  const int col0 = sh_range[0], ncols = sh_range[1];
-
-  if (warp == consumers) {
-    // ---- producer: one lane keeps the ring full ----
-    if (lane == 0 && ncols > 0) {
-      const uint64_t policy = ptx::policy_evict_first();
-      const uint32_t logit_bytes = static_cast<uint32_t>(ncols) * A * 4u;
-      const uint32_t oper_bytes = static_cast<uint32_t>(ncols) * 4u;
-      const uint32_t tx = 2u * logit_bytes + (a.discounts ? 4u : 3u) * oper_bytes;
-      for (int it = 0; it < T; ++it) {
-        const int s = it % depth, n = it / depth;
-        if (n > 0) ptx::mbar_wait(empty_bars + 8u * s, (n - 1) & 1);
-        const int t = T - 1 - it;
-        const uint32_t bar = full_bars + 8u * s;
-        const uint32_t dst = ring_u32 + static_cast<uint32_t>(s) * slot_floats * 4u;
-        const size_t e0 = static_cast<size_t>(t) * B + col0;
-        ptx::mbar_arrive_expect_tx(bar, tx);
-        ptx::bulk_g2s(dst, a.blog + e0 * A, logit_bytes, bar, policy);
-        ptx::bulk_g2s(dst + cols * A * 4u, a.tlog + e0 * A, logit_bytes, bar, policy);
-        const uint32_t op = dst + 2u * cols * A * 4u;
-        ptx::bulk_g2s(op, a.actions + e0, oper_bytes, bar, policy);
-        if (a.discounts) ptx::bulk_g2s(op + cols * 4u, a.discounts + e0, oper_bytes, bar, policy);
-        ptx::bulk_g2s(op + 2u * cols * 4u, a.rewards + e0, oper_bytes, bar, policy);
-        ptx::bulk_g2s(op + 3u * cols * 4u, a.values + e0, oper_bytes, bar, policy);
-      }
-    }
-  } else if (ncols > 0) {
-    // ---- consumers ----
-    const int g = warp % NG, r = warp / NG;
-    const int j = 32 * g + lane;  // column within the tile
-    const bool active = j < ncols;
-    const int b = col0 + (active ? j : 0);
-    const int nb = max(0, min(32, ncols - 32 * g));  // columns of this group
-    const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
-    const bool need_softmax = GRADS || a.partials != nullptr;
-    float* stage_base = staging + static_cast<size_t>(warp) * args.staging_bufs * 32 * A;
-    int stage_sel = 0;
-
-    math::Carry carry;  // R == 1: lives here across steps
-    carry.acc = 0.0f;
-    carry.v_next = active ? a.bootstrap[b] : 0.0f;
-    carry.vs_next = carry.v_next;
-    math::LossSums sums = {0.0, 0.0, 0.0};
-    // `done` flags (experiment.py:384) come straight from global memory, one
-    // owned step ahead.
-    uint8_t done_next = 0;
-    if (a.done && active && r < T) done_next = a.done[static_cast<size_t>(T - 1 - r) * B + b];
-
-    for (int it = r; it < T; it += R) {
-      const int t = T - 1 - it;
-      const size_t e = static_cast<size_t>(t) * B + b;
-      const int s = it % depth;
-      const uint8_t done_cur = done_next;
-      if (a.done && active && it + R < T) done_next = a.done[e - static_cast<size_t>(R) * B];
-
-      ptx::mbar_wait(full_bars + 8u * s, (it / depth) & 1);
-      const float* slot = ring + static_cast<size_t>(s) * slot_floats;
-      const float* xb_row = slot + j * A;
-      const float* xt_row = slot + cols * A + j * A;
-      const float* op = slot + 2 * cols * A;
-
-      // ---- phase A: everything that does not depend on step t+1 ----
-      int act = 0;
-      float disc = 0.0f, rew = 0.0f, val = 0.0f, xa_t = 0.0f, xa_b = 0.0f;
-      math::RowStats st = {0.0f, 1.0f, 0.0f}, sb = {0.0f, 1.0f, 0.0f};
-      float x[A_CT > 0 ? A_CT : 1], ex[A_CT > 0 ? A_CT : 1];  // target row, its exp terms
-      if (active) {
-        act = __float_as_int(op[j]);
-        act = min(max(act, 0), A - 1);
-        disc = a.done ? (done_cur ? 0.0f : a.discounting) : op[cols + j];
-        rew = op[2 * cols + j];
-        val = op[3 * cols + j];
-        xa_t = xt_row[act];
-        xa_b = xb_row[act];
-        if constexpr (A_CT > 0) {
-          float xb[A_CT];
-          load_row(xb, xb_row);
-          sb = math::row_stats(xb);
-          load_row(x, xt_row);
-        }
-      }
-      if constexpr (A_CT > 0) {
-        // Rows are in registers: give the slot back to the producer.
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(empty_bars + 8u * s);
-      }
-      float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f, entropy = 0.0f, inv_sum = 0.0f;
-      math::Weights w = {0.0f, 0.0f, 0.0f};
-      if (active) {
-        rew = math::clip_reward(rew, a.reward_clip_mode);
-        if constexpr (A_CT > 0) {
-          st = math::row_stats(x, ex);
-        } else {
-          st = math::smem_row_stats(xt_row, A);
-          sb = math::smem_row_stats(xb_row, A);
-        }
-        t_lp = math::action_log_prob(xa_t, st);
-        b_lp = math::action_log_prob(xa_b, sb);
-        log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
-        w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
-        if (need_softmax) {
-          inv_sum = __frcp_rn(st.sum);
-          if constexpr (A_CT > 0) entropy = math::row_entropy(x, ex, st, inv_sum);
-          else entropy = math::smem_row_entropy(xt_row, A, st, inv_sum);
-        }
-      }
-
-      // ---- phase B: the V-trace step (vtrace.py:243-276); needs step t+1 ----
-      if (R > 1 && it > 0) {
-        // n-th use of this warp's carry slot (step 0 of the tile has none)
-        const int use = it / R - (r == 0 ? 1 : 0);
-        ptx::mbar_wait(carry_bars + 8u * warp, use & 1);
-        const float* cb = carry_buf + warp * 96;
-        carry.acc = cb[lane], carry.v_next = cb[32 + lane], carry.vs_next = cb[64 + lane];
-      }
-      float vs, pg;
-      math::vtrace_step(w, rew, disc, val, carry, vs, pg);
-      if (R > 1 && it + 1 < T) {
-        const int nw = (r + 1 == R ? 0 : r + 1) * NG + g;  // owner of step it+1
-        float* cb = carry_buf + nw * 96;
-        cb[lane] = carry.acc, cb[32 + lane] = carry.v_next, cb[64 + lane] = carry.vs_next;
-        ptx::mbar_arrive(carry_bars + 8u * nw);
-      }
-
-      // ---- phase C: outputs, gradient row, loss terms ----
-      float* orow_base = stage_base + stage_sel * 32 * A;
-      float* orow = orow_base + lane * A;
-      if (GRADS) {
-        // the bulk store that last read this staging row must be done with it
-        if (lane == 0) {
-          if (args.staging_bufs == 2) ptx::bulk_wait_read<1>();
-          else ptx::bulk_wait_read<0>();
-        }
-        __syncwarp();
-      }
-      if (active) {
-        if (a.vs) a.vs[e] = vs;
-        if (a.pg) a.pg[e] = pg;
-        if (a.log_rhos) a.log_rhos[e] = log_rho;
-        if (a.b_lp) a.b_lp[e] = b_lp;
-        if (a.t_lp) a.t_lp[e] = t_lp;
-        if (GRADS) {
-          // d/dlogits = (p - onehot) pg_adv + entropy_cost p (log p + H)
-          const float ka = __fmul_rn(a.entropy_cost, inv_sum);
-          const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
-          if constexpr (A_CT > 0) {
-            math::row_gradient(ex, x, ka, kb);
-            store_row(orow, ex);
-          } else {
-            math::smem_row_gradient(orow, xt_row, A, st, ka, kb);
-          }
-          orow[act] = __fsub_rn(orow[act], pg);  // the -onehot(a) * pg_adv term
-          if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
-        }
-        if (a.partials) sums.add(t_lp, pg, vs, val, entropy);
-      }
-      if (GRADS) {
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0 && nb > 0) {
-          ptx::bulk_s2g(a.d_logits + (static_cast<size_t>(t) * B + col0 + 32 * g) * A,
-                        ptx::smem_u32(orow_base), row_bytes);
-          ptx::bulk_commit();
-        }
-        if (args.staging_bufs == 2) stage_sel ^= 1;
-      }
-      if constexpr (A_CT == 0) {
-        // run-time A re-reads the rows from the slot: release it only now
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(empty_bars + 8u * s);
-      }
-    }
-
-    if (a.partials) {
-      double* mine = lane_sums + static_cast<size_t>(warp) * 96;
-      mine[lane] = sums.pg, mine[32 + lane] = sums.baseline, mine[64 + lane] = sums.entropy;
-    }
-    if (GRADS && lane == 0) ptx::bulk_wait<0>();
-  }
-
-  if (a.partials) {
-    // One partial per granule of 4 columns, summed over the relay warps and then
-    // over the 4 lanes in a fixed order: the same numbers however the batch
-    // was cut into tiles.
-    __syncthreads();
-    for (int q = threadIdx.x; q < (ncols >> 2); q += blockDim.x) {
-      const int g = (4 * q) >> 5, l0 = (4 * q) & 31;
-      double p[3] = {0.0, 0.0, 0.0};
-      for (int l = l0; l < l0 + 4; ++l)
-        for (int r = 0; r < R; ++r) {
-          const double* src = lane_sums + static_cast<size_t>(r * NG + g) * 96;
-          p[0] += src[l], p[1] += src[32 + l], p[2] += src[64 + l];
-        }
-      double* out = a.partials + 3 * (static_cast<size_t>(col0 >> 2) + q);
-      out[0] = p[0], out[1] = p[1], out[2] = p[2];
-    }
-  }
-  if (a.partials && args.cursor && (a.losses || a.losses_f64)) {
-    // Second stage inside the same launch: the tile that finishes last (a
-    // ticket, the only other atomic besides the cursor; no value is ever
-    // accumulated atomically) sums all granule partials in a fixed order.
-    __shared__ int sh_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) sh_last = atomicAdd(args.cursor + 1, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (sh_last) {
-      __threadfence();
-      const volatile double* parts = a.partials;
-      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int i = threadIdx.x; i < total_gran; i += blockDim.x)
-        p0 += parts[3 * i], p1 += parts[3 * i + 1], p2 += parts[3 * i + 2];
-      p0 = warp_sum_fixed(p0), p1 = warp_sum_fixed(p1), p2 = warp_sum_fixed(p2);
-      double* warp_tot = lane_sums;  // free again: every tile partial has been written
-      if (lane == 0) warp_tot[3 * warp] = p0, warp_tot[3 * warp + 1] = p1, warp_tot[3 * warp + 2] = p2;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        double pg = 0.0, bl = 0.0, ent = 0.0;
-        for (int w = 0; w <= consumers; ++w)
-          pg += warp_tot[3 * w], bl += warp_tot[3 * w + 1], ent += warp_tot[3 * w + 2];
-        const double total = pg + static_cast<double>(a.baseline_cost) * bl +
-                             static_cast<double>(a.entropy_cost) * ent;
-        if (a.losses) {
-          a.losses[0] = static_cast<float>(pg), a.losses[1] = static_cast<float>(bl);
-          a.losses[2] = static_cast<float>(ent), a.losses[3] = static_cast<float>(total);
-        }
-        if (a.losses_f64)
-          a.losses_f64[0] = pg, a.losses_f64[1] = bl, a.losses_f64[2] = ent, a.losses_f64[3] = total;
-      }
-    }
-  }
-  if (threadIdx.x == 0 && ncols > 0) {
-    const unsigned int sm = sm_id();
-    const unsigned long long dt = global_timer_ns() - t_begin;
-    // Tiles shorter than 20 us measure launch latency, not the SM: leave the table alone.
-    if (sm < kMaxSms && dt > 20000) {
-      const float speed = static_cast<float>(ncols) * T / static_cast<float>(dt);
-      const float old = g_sm_speed[sm];
-      g_sm_speed[sm] = old > 0.0f ? 0.5f * (old + speed) : speed;
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------
-// K2: item-parallel kernel for small batches.  One CTA per batch column, one
-// thread per time step: every thread loads its own two logits rows straight
-// from global memory, does everything that does not depend on step t+1, and
-// leaves (gain_t, delta_t) in shared memory; thread 0 then runs the recurrence
-// acc_t = gain_t acc_{t+1} + delta_t over the T entries (T dependent FMAs, a
-// fraction of a microsecond) and every thread finishes its own step.  The
-// arithmetic is the same sequence of operations as in K1, so the results are
-// bit-identical to K1's.  With B columns x T steps all in flight at once, a
-// small batch costs one memory round trip instead of T sequential steps.
-// Needs T <= kItemMaxSteps and a compile-time A.
-// ---------------------------------------------------------------------------
-constexpr int kItemMaxSteps = 256;
-constexpr int kItemMaxColumns = 16384;  // K2 writes one loss partial per column
-
-template <int N>
-__device__ __forceinline__ void load_row_global(float (&x)[N], const float* row) {
-  if (N % 2 == 0 && (reinterpret_cast<uintptr_t>(row) & 7) == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 2; ++i) {
-      const float2 v = __ldg(reinterpret_cast<const float2*>(row) + i);
-      x[2 * i] = v.x, x[2 * i + 1] = v.y;
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < N; ++i) x[i] = __ldg(row + i);
-  }
-}
-
-template <int N>
-__device__ __forceinline__ void store_row_global(float* row, const float (&x)[N]) {
-  if (N % 2 == 0 && (reinterpret_cast<uintptr_t>(row) & 7) == 0) {
-#pragma unroll
-    for (int i = 0; i < N / 2; ++i) reinterpret_cast<float2*>(row)[i] = make_float2(x[2 * i], x[2 * i + 1]);
-  } else {
-#pragma unroll
-    for (int i = 0; i < N; ++i) row[i] = x[i];
-  }
-}
-
-template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(kItemMaxSteps) fused_item_kernel(const __grid_constant__ FusedArgs a) {
-  static_assert(A_CT > 0, "the item kernel keeps rows in registers");
-  __shared__ float sh_gain[kItemMaxSteps], sh_delta[kItemMaxSteps], sh_acc[kItemMaxSteps];
-  __shared__ double sh_sums[3][kItemMaxSteps / 32];
-  const int T = a.T, B = a.B;
-  const int k = threadIdx.x;  // step index from the end: t = T-1-k
-  const int b = blockIdx.x;
-  const bool active = k < T;
-  const int t = T - 1 - (active ? k : 0);
-  const size_t e = static_cast<size_t>(t) * B + b;
-  const bool need_softmax = GRADS || a.partials != nullptr;
-
-  float disc = 0.0f, rew = 0.0f, val = 0.0f, v_next = 0.0f, t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
-  float entropy = 0.0f, inv_sum = 0.0f;
-  int act = 0;
-  math::Weights w = {0.0f, 0.0f, 0.0f};
-  float x[A_CT], ex[A_CT];
-  if (active) {
-    act = min(max(__ldg(a.actions + e), 0), A_CT - 1);
-    disc = a.done ? (a.done[e] ? 0.0f : a.discounting) : __ldg(a.discounts + e);
-    rew = math::clip_reward(__ldg(a.rewards + e), a.reward_clip_mode);
-    val = __ldg(a.values + e);
-    v_next = k == 0 ? __ldg(a.bootstrap + b) : __ldg(a.values + e + B);  // vtrace.py:243-244
-    float xb[A_CT];
-    load_row_global(xb, a.blog + e * A_CT);
-    load_row_global(x, a.tlog + e * A_CT);
-    const float xa_b = __ldg(a.blog + e * A_CT + act), xa_t = __ldg(a.tlog + e * A_CT + act);
-    const math::RowStats sb = math::row_stats(xb);
-    const math::RowStats st = math::row_stats(x, ex);
-    t_lp = math::action_log_prob(xa_t, st);
-    b_lp = math::action_log_prob(xa_b, sb);
-    log_rho = __fsub_rn(t_lp, b_lp);  // vtrace.py:147
-    w = math::importance_weights(log_rho, a.flags, a.clip_rho, a.clip_pg_rho);
-    if (need_softmax) {
-      inv_sum = __frcp_rn(st.sum);
-      entropy = math::row_entropy(x, ex, st, inv_sum);
-    }
-    sh_gain[k] = math::step_gain(w, disc);
-    sh_delta[k] = math::step_delta(w, rew, disc, val, v_next);
-  }
-  __syncthreads();
-  if (k == 0) {
-    float acc = 0.0f;  // vtrace.py:256
-    for (int i = 0; i < T; ++i) {
-      acc = math::step_acc(sh_gain[i], acc, sh_delta[i]);
-      sh_acc[i] = acc;
-    }
-  }
-  __syncthreads();
-
-  double s_pg = 0.0, s_bl = 0.0, s_ent = 0.0;
-  if (active) {
-    const float vs = __fadd_rn(sh_acc[k], val);  // vtrace.py:265
-    // vs_{t+1} = acc_{t+1} + V(x_{t+1}); bootstrap_value past the end (:268-269)
-    const float vs_next = k == 0 ? v_next : __fadd_rn(sh_acc[k - 1], v_next);
-    const float pg = math::step_pg(w, rew, disc, val, vs_next);
-    if (a.vs) a.vs[e] = vs;
-    if (a.pg) a.pg[e] = pg;
-    if (a.log_rhos) a.log_rhos[e] = log_rho;
-    if (a.b_lp) a.b_lp[e] = b_lp;
-    if (a.t_lp) a.t_lp[e] = t_lp;
-    if (GRADS) {
-      const float ka = __fmul_rn(a.entropy_cost, inv_sum);
-      const float kb = __fmul_rn(__fmaf_rn(a.entropy_cost, entropy, pg), inv_sum);
-      math::row_gradient(ex, x, ka, kb);
-#pragma unroll
-      for (int i = 0; i < A_CT; ++i)
-        if (i == act) ex[i] = __fsub_rn(ex[i], pg);  // the -onehot(a) * pg_adv term
-      store_row_global(a.d_logits + e * A_CT, ex);
-      if (a.d_values) a.d_values[e] = __fmul_rn(a.baseline_cost, __fsub_rn(val, vs));
-    }
-    if (a.partials) {
-      math::LossSums one = {0.0, 0.0, 0.0};
-      one.add(t_lp, pg, vs, val, entropy);
-      s_pg = one.pg, s_bl = one.baseline, s_ent = one.entropy;
-    }
-  }
-  if (a.partials) {
-    // fixed order: xor tree inside each warp, then the warps in index order
-    s_pg = warp_sum_fixed(s_pg), s_bl = warp_sum_fixed(s_bl), s_ent = warp_sum_fixed(s_ent);
-    if ((k & 31) == 0) sh_sums[0][k >> 5] = s_pg, sh_sums[1][k >> 5] = s_bl, sh_sums[2][k >> 5] = s_ent;
-    __syncthreads();
-    if (k == 0) {
-      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int wi = 0; wi < (blockDim.x >> 5); ++wi)
-        p0 += sh_sums[0][wi], p1 += sh_sums[1][wi], p2 += sh_sums[2][wi];
-      double* out = a.partials + 3 * static_cast<size_t>(b);
-      out[0] = p0, out[1] = p1, out[2] = p2;
-    }
-  }
-}
 
 // K3: second stage of the loss reduction.  One block, fixed summation order.
 __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __restrict__ partials,
@@ -1628,3 +582,4 @@ extern "C" int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void
     q.path = VTR_PATH_COLUMN;
   return vtr_from_logits_fused_f32(&q, scratch, scratch_bytes, stream);
 }
+
