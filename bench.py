@@ -266,7 +266,9 @@ def run_gpu(args):
   if world > 1:
     dist.init_process_group('nccl', device_id=device)
   T, B, A = args.T, args.B, args.A
-  K, W = args.steps, max(args.warmup, 3)
+  # at least 10 untimed steps: the per-SM speed table behind the tile sizes
+  # settles within a handful of calls
+  K, W = args.steps, max(args.warmup, 10)
 
   inp = synthetic_on_device(T, B, A, 1000 * rank + 1, device)
   call = FusedCall(inp, T, B, A, device)
