@@ -326,7 +326,6 @@ def run_gpu(args):
   t_end.record()
   barrier()
   total_ms = t_begin.elapsed_time(t_end)
-  kernel_ms = [total_ms / K]
   # keep the GPU busy a little longer if the region was too short to sample
   if sampler.ok and len(sampler.samples) < 5:
     t0 = time.perf_counter()
@@ -343,12 +342,7 @@ def run_gpu(args):
     t = torch.tensor([total_ms], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms = float(t.item())
-    km = torch.tensor([statistics.mean(kernel_ms)], dtype=torch.float64,
-                      device=device)
-    dist.all_reduce(km, op=dist.ReduceOp.MAX)
-    kernel_mean_ms = float(km.item())
-  else:
-    kernel_mean_ms = statistics.mean(kernel_ms)
+  kernel_mean_ms = total_ms / K      # max over ranks of the mean time per call
   value = T * B * world * K / (total_ms * 1e-3)
 
   # ---- end to end through the public API with host buffers ---------------

@@ -19,8 +19,6 @@ FLAG_NO_CLIP_PG_RHO = 2
 REWARD_CLIP_MODES = {None: 0, 'none': 0, 'abs_one': 1, 'soft_asymmetric': 2}
 PATHS = {None: 0, 'auto': 0, 'column': 1, 'sm_tile': 2, 'item': 3}
 
-_c_float_p = ctypes.c_void_p  # raw device pointers travel as void*
-
 
 class FusedParams(ctypes.Structure):
   """Mirror of `struct vtr_fused_params` (include/vtrace_b200.h)."""
