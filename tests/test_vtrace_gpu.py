@@ -215,7 +215,7 @@ def test_fused_matches_oracle(api, T, B, A, path):
     (5, 4, 3), (100, 32, 9), (20, 512, 18), (1, 4, 1), (2, 8, 4), (3, 64, 6),
     (7, 68, 5), (40, 36, 7), (9, 100, 32), (6, 36, 100), (4, 4, 256),
     (50, 132, 9), (100, 1000, 18), (100, 4736, 18), (30, 9000, 9),
-    (17, 38000, 18),
+    (17, 38000, 18), (4, 70000, 3), (3, 140000, 4),
 ])
 def test_sm_tile_kernel_matches_oracle(api, T, B, A):
   """K1c explicitly (B % 4 == 0): every grid shape of its launch heuristics --
@@ -514,3 +514,31 @@ def test_learner_loss_on_t_plus_1_tensors(api, T, B, A, clip):
   assert_close(_np(baseline_t.grad[:-1]), ref.d_values, TOL, 'd_baseline')
   assert float(logits_t.grad[-1].abs().max()) == 0.0
   assert float(baseline_t.grad[-1].abs().max()) == 0.0
+
+
+def test_many_tiles_and_graceful_fallback(api):
+  """Grids far beyond one wave on the 32-column-tile path, and a shape whose
+  ring does not fit the per-SM kernel (A=100, 88 columns per SM): the
+  automatic choice must fall back to the 32-column tiles, not fail."""
+  _, experiment = api
+  _check_fused(experiment, oracle.synthetic_inputs(4, 70000, 3, seed=70), path='column')
+  _check_fused(experiment, oracle.synthetic_inputs(6, 9600, 100, seed=71), path='auto')
+
+
+def test_from_logits_wide_batch_without_losses(api):
+  """vtrace.from_logits alone (no losses, no gradients, no workspace) on a
+  batch wide enough for the per-SM kernel, which then deals tiles evenly."""
+  vtrace, _ = api
+  inp = oracle.synthetic_inputs(40, 16384, 9, seed=40)
+  out = vtrace.from_logits(*[inp[k] for k in FUSED_KEYS])
+  ref = oracle.from_logits(*[inp[k] for k in FUSED_KEYS])
+  for f in out._fields:
+    assert_close(_np(getattr(out, f)), getattr(ref, f), TOL, f)
+
+
+def test_done_and_clipping_on_the_item_kernel(api):
+  _, experiment = api
+  inp = oracle.synthetic_inputs(25, 68, 9, seed=23, reward_clipping=None)
+  inp['rewards'] = inp['raw_rewards']
+  _check_fused(experiment, inp, reward_clipping='abs_one', done_np=inp['done'],
+               discounting=0.95, path='item')
