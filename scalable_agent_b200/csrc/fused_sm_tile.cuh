@@ -51,6 +51,7 @@ struct SmTileArgs {
   int num_sm;        // SMs of the device
   int waves;         // tiles per SM (grid = num_sm * waves) when balancing
   unsigned int* cursor;  // zeroed column cursor for speed-weighted tiles, or null
+  float smoothing;       // weight of the newest measurement in the speed table
 };
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
@@ -380,10 +381,24 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
     __syncthreads();
     if (sh_last) {
       __threadfence();
-      const volatile double* parts = a.partials;
+      // Other tiles' partials are read from L2 (ld.global.cg: this SM's L1 has
+      // never seen them); eight granules per thread are in flight at a time
+      // and are added in index order.
+      const double* parts = a.partials;
       double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int i = threadIdx.x; i < total_gran; i += blockDim.x)
-        p0 += parts[3 * i], p1 += parts[3 * i + 1], p2 += parts[3 * i + 2];
+      for (int i0 = threadIdx.x; i0 < total_gran; i0 += 8 * blockDim.x) {
+        double v[8][3];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = i0 + u * blockDim.x;
+          const bool in = i < total_gran;
+          v[u][0] = in ? __ldcg(parts + 3 * i) : 0.0;
+          v[u][1] = in ? __ldcg(parts + 3 * i + 1) : 0.0;
+          v[u][2] = in ? __ldcg(parts + 3 * i + 2) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) p0 += v[u][0], p1 += v[u][1], p2 += v[u][2];
+      }
       p0 = warp_sum_fixed(p0), p1 = warp_sum_fixed(p1), p2 = warp_sum_fixed(p2);
       double* warp_tot = lane_sums;  // free again: every tile partial has been written
       if (lane == 0) warp_tot[3 * warp] = p0, warp_tot[3 * warp + 1] = p1, warp_tot[3 * warp + 2] = p2;
@@ -410,7 +425,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
     if (sm < kMaxSms && dt > 20000) {
       const float speed = static_cast<float>(ncols) * T / static_cast<float>(dt);
       const float old = g_sm_speed[sm];
-      g_sm_speed[sm] = old > 0.0f ? 0.5f * (old + speed) : speed;
+      g_sm_speed[sm] = old > 0.0f ? old + args.smoothing * (speed - old) : speed;
     }
   }
 }

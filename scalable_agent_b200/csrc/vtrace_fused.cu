@@ -250,6 +250,8 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   args.num_sm = sm;
   args.waves = waves;
   args.cursor = balance ? static_cast<unsigned int*>(header) : nullptr;
+  args.smoothing = 0.5f;
+  if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
   if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
   *losses_done = balance;
 
