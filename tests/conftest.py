@@ -14,6 +14,13 @@ GOLDEN_PATH = os.path.join(ROOT, 'tests', 'golden', 'vtrace_golden.npz')
 def pytest_configure(config):
   config.addinivalue_line(
       'markers', 'gpu: needs a CUDA device (run on the B200 box via gpurun)')
+  # The C-ABI library is a build artefact (git-ignored).  Build it once if a
+  # fresh checkout has none: nvcc cross-compiles sm_100a without a GPU.
+  lib = os.path.join(ROOT, 'scalable_agent_b200', 'lib', 'libvtrace_b200.so')
+  if not os.path.exists(lib) and not os.environ.get('VTRACE_B200_LIB'):
+    import subprocess
+    subprocess.run(['make', '-C', os.path.join(ROOT, 'scalable_agent_b200', 'csrc'),
+                    '-j', str(max(1, min(8, os.cpu_count() or 1)))], check=True)
 
 
 class Golden(object):
