@@ -130,11 +130,12 @@ typedef struct vtr_fused_params {
   double* losses_f64; /* double[4], may be NULL */
 } vtr_fused_params;
 
-/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): a
-   64-byte header (tile cursor and finish ticket of the per-SM kernel; the
-   library zeroes it itself) followed by the loss partials of the deterministic
-   two-stage reduction, one double[3] per 32-column tile or per 4-column
-   granule depending on the kernel.  Returns 0 on invalid sizes. */
+/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): an
+   8 KB header (tile cursor, tickets and group partials of the per-SM kernel;
+   the library zeroes what must be zero itself) followed by the loss partials
+   of the deterministic staged reduction, one double[3] per 32-column tile,
+   per 4-column granule or per column depending on the kernel.  Returns 0 on
+   invalid sizes. */
 size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A);
 
 /* The fused pass.  `workspace` must hold vtr_fused_workspace_bytes() bytes,
@@ -159,7 +160,7 @@ int vtr_fused_describe(const vtr_fused_params* p, int have_workspace, int* num_k
    temporary allocator, or a learner running in a process where cudaMalloc is
    forbidden after start-up because the memory pool owns the whole GPU and a
    cudaMalloc would fail or stall the other streams by synchronising the
-   device.  The tile partials go to a 192 KiB array built into the library
+   device.  The tile partials go to a 200 KiB array built into the library
    (every GPU that loads the library holds it until the process exits); the
    caller still passes all inputs and outputs in `p`.  Results are identical to
    vtr_from_logits_fused_f32.

@@ -28,7 +28,7 @@ namespace vtr {
 //              rewards[cols] values[cols], cols = 32*groups
 //   staging    per consumer warp, staging_bufs x 32*A floats   (GRADS only)
 //   carry      per consumer warp 3 x 32 floats
-//   sums       per consumer warp 3 doubles
+//   sums       per consumer warp 3 x 32 doubles (per-lane loss sums)
 // ---------------------------------------------------------------------------
 constexpr int kSmBarrierBytes = 512;
 constexpr int kSmMaxConsumerWarps = 18;
@@ -50,8 +50,11 @@ struct SmTileArgs {
   int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
   int num_sm;        // SMs of the device
   int waves;         // tiles per SM (grid = num_sm * waves) when balancing
-  unsigned int* cursor;  // zeroed column cursor for speed-weighted tiles, or null
-  float smoothing;       // weight of the newest measurement in the speed table
+  unsigned int* cursor;  // workspace header (zeroed): [0] column cursor, [1] finished
+                         // groups, [16 + k] granules of group k written so far; or null
+  double* group_partials;  // [groups][3], second level of the loss reduction
+  int group_gran;          // granules (of 4 columns) per reduction group
+  float smoothing;         // weight of the newest measurement in the speed table
 };
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
@@ -370,52 +373,71 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
       out[0] = p[0], out[1] = p[1], out[2] = p[2];
     }
   }
-  if (a.partials && args.cursor && (a.losses || a.losses_f64)) {
-    // Second stage inside the same launch: the tile that finishes last (a
-    // ticket, the only other atomic besides the cursor; no value is ever
-    // accumulated atomically) sums all granule partials in a fixed order.
-    __shared__ int sh_last;
+  if (a.partials && args.cursor && (a.losses || a.losses_f64) && ncols > 0) {
+    // Second and third stage inside the same launch, without a pass over all
+    // partials by one SM.  Granules are grouped in fixed ranges of
+    // `group_gran`; a tile adds the number of granules it wrote to each group
+    // it overlaps (a ticket: no value is ever accumulated atomically), and the
+    // tile that completes a group sums that group's granule partials in index
+    // order.  Whoever completes the last group sums the group partials in
+    // index order.  Neither level depends on how the batch was cut into tiles.
+    __shared__ int sh_flag;
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) sh_last = atomicAdd(args.cursor + 1, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (sh_last) {
-      __threadfence();
-      // Other tiles' partials are read from L2 (ld.global.cg: this SM's L1 has
-      // never seen them); eight granules per thread are in flight at a time
-      // and are added in index order.
-      const double* parts = a.partials;
-      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int i0 = threadIdx.x; i0 < total_gran; i0 += 8 * blockDim.x) {
-        double v[8][3];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int i = i0 + u * blockDim.x;
-          const bool in = i < total_gran;
-          v[u][0] = in ? __ldcg(parts + 3 * i) : 0.0;
-          v[u][1] = in ? __ldcg(parts + 3 * i + 1) : 0.0;
-          v[u][2] = in ? __ldcg(parts + 3 * i + 2) : 0.0;
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) p0 += v[u][0], p1 += v[u][1], p2 += v[u][2];
-      }
-      p0 = warp_sum_fixed(p0), p1 = warp_sum_fixed(p1), p2 = warp_sum_fixed(p2);
-      double* warp_tot = lane_sums;  // free again: every tile partial has been written
-      if (lane == 0) warp_tot[3 * warp] = p0, warp_tot[3 * warp + 1] = p1, warp_tot[3 * warp + 2] = p2;
-      __syncthreads();
+    const int G = args.group_gran;
+    const int gran0 = col0 >> 2, gran1 = (col0 + ncols) >> 2;  // this tile's granules [gran0, gran1)
+    const int num_groups = (total_gran + G - 1) / G;
+    for (int grp = gran0 / G; grp <= (gran1 - 1) / G; ++grp) {
+      const int lo = grp * G, hi = min(total_gran, lo + G);
       if (threadIdx.x == 0) {
-        double pg = 0.0, bl = 0.0, ent = 0.0;
-        for (int w = 0; w <= consumers; ++w)
-          pg += warp_tot[3 * w], bl += warp_tot[3 * w + 1], ent += warp_tot[3 * w + 2];
-        const double total = pg + static_cast<double>(a.baseline_cost) * bl +
-                             static_cast<double>(a.entropy_cost) * ent;
-        if (a.losses) {
-          a.losses[0] = static_cast<float>(pg), a.losses[1] = static_cast<float>(bl);
-          a.losses[2] = static_cast<float>(ent), a.losses[3] = static_cast<float>(total);
-        }
-        if (a.losses_f64)
-          a.losses_f64[0] = pg, a.losses_f64[1] = bl, a.losses_f64[2] = ent, a.losses_f64[3] = total;
+        const unsigned int mine = static_cast<unsigned int>(min(gran1, hi) - max(gran0, lo));
+        const unsigned int before = atomicAdd(args.cursor + 16 + grp, mine);
+        sh_flag = before + mine == static_cast<unsigned int>(hi - lo);
       }
+      __syncthreads();
+      if (sh_flag) {
+        __threadfence();
+        // ld.global.cg: other tiles wrote these; this SM's L1 has never seen them
+        double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+        for (int i = lo + threadIdx.x; i < hi; i += blockDim.x)
+          p0 += __ldcg(a.partials + 3 * i), p1 += __ldcg(a.partials + 3 * i + 1),
+              p2 += __ldcg(a.partials + 3 * i + 2);
+        p0 = warp_sum_fixed(p0), p1 = warp_sum_fixed(p1), p2 = warp_sum_fixed(p2);
+        double* warp_tot = lane_sums;  // free: this tile's granule partials are written
+        if (lane == 0) warp_tot[3 * warp] = p0, warp_tot[3 * warp + 1] = p1, warp_tot[3 * warp + 2] = p2;
+        __syncthreads();
+        if (warp == 0) {
+          double g0 = 0.0, g1 = 0.0, g2 = 0.0;
+          if (lane == 0) {
+            for (int w = 0; w <= consumers; ++w)
+              g0 += warp_tot[3 * w], g1 += warp_tot[3 * w + 1], g2 += warp_tot[3 * w + 2];
+            double* out = args.group_partials + 3 * grp;
+            out[0] = g0, out[1] = g1, out[2] = g2;
+            __threadfence();
+            sh_flag = atomicAdd(args.cursor + 1, 1u) == static_cast<unsigned int>(num_groups - 1);
+          }
+          __syncwarp();
+          if (sh_flag) {  // every group is complete: the final sum, in group order
+            __threadfence();
+            double pg = 0.0, bl = 0.0, ent = 0.0;
+            for (int k = lane; k < num_groups; k += 32)
+              pg += __ldcg(args.group_partials + 3 * k), bl += __ldcg(args.group_partials + 3 * k + 1),
+                  ent += __ldcg(args.group_partials + 3 * k + 2);
+            pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
+            if (lane == 0) {
+              const double total = pg + static_cast<double>(a.baseline_cost) * bl +
+                                   static_cast<double>(a.entropy_cost) * ent;
+              if (a.losses) {
+                a.losses[0] = static_cast<float>(pg), a.losses[1] = static_cast<float>(bl);
+                a.losses[2] = static_cast<float>(ent), a.losses[3] = static_cast<float>(total);
+              }
+              if (a.losses_f64)
+                a.losses_f64[0] = pg, a.losses_f64[1] = bl, a.losses_f64[2] = ent, a.losses_f64[3] = total;
+            }
+          }
+        }
+      }
+      __syncthreads();
     }
   }
   if (threadIdx.x == 0 && ncols > 0) {

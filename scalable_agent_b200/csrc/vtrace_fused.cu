@@ -207,9 +207,14 @@ static int dispatch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaS
   }
 }
 
-// Workspace layout (vtr_fused_workspace_bytes): a 64-byte header whose first
-// word is K1c's column cursor, then the loss partials.
-constexpr size_t kWorkspaceHeaderBytes = 64;
+// Workspace layout (vtr_fused_workspace_bytes): an 8 KB header -- K1c's column
+// cursor, its finished-group ticket and per-group granule counters in the
+// first KB (zeroed by the library before every K1c launch), its group
+// partials after that -- then the loss partials.
+constexpr size_t kWorkspaceHeaderBytes = 8192;  // counters in [0,1024), group partials after
+constexpr size_t kWorkspaceCounterBytes = 1024;
+constexpr int kMaxReductionGroups = 240;
+constexpr int kReductionGroupGranules = 512;
 
 // K1c launch: `*num_partials` = partials written (one per granule of 4 columns).
 // `header` is the 64-byte workspace header, or null when the caller gave no
@@ -250,6 +255,12 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   args.num_sm = sm;
   args.waves = waves;
   args.cursor = balance ? static_cast<unsigned int*>(header) : nullptr;
+  args.group_partials = balance ? reinterpret_cast<double*>(static_cast<char*>(header) +
+                                                            kWorkspaceCounterBytes)
+                                : nullptr;
+  args.group_gran = kReductionGroupGranules;
+  if ((total_gran + args.group_gran - 1) / args.group_gran > kMaxReductionGroups)
+    args.group_gran = (total_gran + kMaxReductionGroups - 1) / kMaxReductionGroups;
   args.smoothing = 0.5f;
   if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
   if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
@@ -294,7 +305,7 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   args.f.depth = static_cast<int>(depth);
   const size_t smem = fixed + depth * slot_bytes;
   if (balance && !g_plan.dry_run)
-    VTR_CUDA_CHECK(cudaMemsetAsync(header, 0, kWorkspaceHeaderBytes, stream));
+    VTR_CUDA_CHECK(cudaMemsetAsync(header, 0, kWorkspaceCounterBytes, stream));
   *num_partials = total_gran;
   return grads ? dispatch_sm_tile<true>(args, grid, smem, stream)
                : dispatch_sm_tile<false>(args, grid, smem, stream);
@@ -527,7 +538,7 @@ extern "C" int vtr_fused_describe(const vtr_fused_params* p, int have_workspace,
 // (it can fail once the pool owns the GPU, and it synchronises the device,
 // stalling the inference streams that share it).  For them the tile partials
 // of the two-stage loss reduction live in the fixed array below instead of a
-// caller buffer.  Every GPU that loads the library carries these 192 KiB until
+// caller buffer.  Every GPU that loads the library carries these 200 KiB until
 // the process exits, whether or not this entry point is ever called.
 // ---------------------------------------------------------------------------
 #include <mutex>

@@ -32,8 +32,8 @@ def test_header_symbols_are_exported_and_bound():
 def test_version_and_sizes():
   lib = _lib.load()
   assert lib.vtr_version() == 100
-  assert lib.vtr_fused_workspace_bytes(100, 32768, 18) >= 64 + 8192 * 24
-  assert lib.vtr_fused_workspace_bytes(5, 2, 3) == 64 + 2 * 24   # K2: one partial per column
+  assert lib.vtr_fused_workspace_bytes(100, 32768, 18) == 8192 + 8192 * 24
+  assert lib.vtr_fused_workspace_bytes(5, 2, 3) == 8192 + 2 * 24   # K2: one partial per column
   assert lib.vtr_fused_workspace_bytes(0, 4, 4) == 0
   assert lib.vtr_loss_workspace_bytes(1) == 8
   assert lib.vtr_loss_workspace_bytes(0) == 0
