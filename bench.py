@@ -279,11 +279,14 @@ def run_gpu(args):
   exchange, exchange_kind = None, 'none'
   if world > 1:
     exchange_kind = 'nccl all_gather'
-    if args.exchange == 'p2p':
+    if args.exchange in ('fused', 'p2p'):
       try:
         from scalable_agent_b200.distributed import LossExchange
         exchange = LossExchange(device)
-        exchange_kind = 'p2p stores over NVLink (vtr_exchange_*), 2 launches'
+        exchange_kind = (
+            'p2p stores over NVLink and the wait for the peers, both inside the fused kernel'
+            if args.exchange == 'fused' else
+            'p2p stores over NVLink (vtr_exchange_*), 2 launches')
       except Exception as e:  # pylint: disable=broad-except
         exchange_kind = 'nccl all_gather (p2p exchange unavailable: %s)' % (
             str(e).splitlines()[0][:80])
@@ -298,7 +301,14 @@ def run_gpu(args):
     dist.all_gather_into_tensor(gathered, call.out['losses'])
     return gathered
 
+  fused_exchange = exchange is not None and args.exchange == 'fused'
+  global_losses = torch.zeros(4, dtype=torch.float32, device=device)
+
   def step():
+    if fused_exchange:
+      exchange.attach(call.p, global_losses)
+      call()
+      return
     call()
     if world > 1:
       exchange_losses()
@@ -429,7 +439,7 @@ def run_gpu(args):
                 'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + '
                        'backward, pinned host inputs'},
         'gpu_launches': (call.launches_per_call +
-                         (2 if exchange is not None else 0)) * K,
+                         (0 if exchange is None or fused_exchange else 2)) * K,
         'clocks': dict(sampler.summary(), sampled=clock_note),
     }
   if world > 1:
@@ -460,7 +470,7 @@ def main():
   ap.add_argument('--B', type=int, default=B_DEFAULT, help='columns per GPU')
   ap.add_argument('--A', type=int, default=A_DEFAULT)
   ap.add_argument('--no-cpu-baseline', action='store_true')
-  ap.add_argument('--exchange', default='p2p', choices=['p2p', 'nccl'],
+  ap.add_argument('--exchange', default='fused', choices=['fused', 'p2p', 'nccl'],
                   help='how the loss scalars are summed over ranks (N > 1)')
   args = ap.parse_args()
   if args.impl == 'reference':

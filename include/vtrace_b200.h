@@ -128,6 +128,22 @@ typedef struct vtr_fused_params {
      [2]=entropy (unweighted, = -sum H), [3]=weighted total.            */
   float* losses;      /* float[4]  */
   double* losses_f64; /* double[4], may be NULL */
+
+  /* Optional, for a batch sharded over the GPUs of one box: publish the four
+     loss scalars to every peer as the last thing the pass does, exactly as
+     vtr_exchange_publish_f32 would (same buffers, same seq rules; see
+     below).  The per-SM kernel does the peer stores itself from the tile that
+     finishes the reduction; on the other kernels the library appends the
+     publish launch.  NULL / 0 = off.  Needs `losses`. */
+  void* const* exchange_peer_buffers; /* HOST array of exchange_world device pointers */
+  int32_t exchange_rank;
+  int32_t exchange_world;
+  uint32_t exchange_seq;
+  uint32_t reserved2;
+  /* float[4] or NULL: if given, the pass also does vtr_exchange_collect_f32's
+     part (wait for every rank's scalars of this seq, at most 2 s, and write
+     their rank-ordered sum here), so a step needs no exchange call at all. */
+  float* exchange_sums;
 } vtr_fused_params;
 
 /* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): an

@@ -50,6 +50,12 @@ class FusedParams(ctypes.Structure):
       ('d_values', ctypes.c_void_p),
       ('losses', ctypes.c_void_p),
       ('losses_f64', ctypes.c_void_p),
+      ('exchange_peer_buffers', ctypes.POINTER(ctypes.c_void_p)),
+      ('exchange_rank', ctypes.c_int32),
+      ('exchange_world', ctypes.c_int32),
+      ('exchange_seq', ctypes.c_uint32),
+      ('reserved2', ctypes.c_uint32),
+      ('exchange_sums', ctypes.c_void_p),
   ]
 
 

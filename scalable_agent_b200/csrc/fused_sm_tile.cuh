@@ -1,5 +1,6 @@
 // K1c of the fused pass (see vtrace_fused.cu).
 #pragma once
+#include "exchange.cuh"
 #include "fused_common.cuh"
 
 namespace vtr {
@@ -55,6 +56,12 @@ struct SmTileArgs {
   double* group_partials;  // [groups][3], second level of the loss reduction
   int group_gran;          // granules (of 4 columns) per reduction group
   float smoothing;         // weight of the newest measurement in the speed table
+  // Loss exchange of a sharded batch, done by the tile that finishes the
+  // reduction (exchange.cuh); ex_world == 0 turns it off.
+  PeerBuffers ex_peers;
+  int ex_rank, ex_world;
+  uint32_t ex_seq;
+  float* ex_sums;  // or null: sum over ranks, collected by the same tile
 };
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
@@ -122,7 +129,7 @@ __device__ __forceinline__ int weighted_share(const SmTileArgs& args, int total_
 }
 
 template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
+__global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     fused_sm_tile_kernel(const __grid_constant__ SmTileArgs args) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const FusedArgs& a = args.f;
@@ -424,9 +431,19 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1))
               pg += __ldcg(args.group_partials + 3 * k), bl += __ldcg(args.group_partials + 3 * k + 1),
                   ent += __ldcg(args.group_partials + 3 * k + 2);
             pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
+            const double total = pg + static_cast<double>(a.baseline_cost) * bl +
+                                 static_cast<double>(a.entropy_cost) * ent;
+            if (lane < args.ex_world) {  // lane r stores this rank's four scalars into peer r
+              exchange_publish4_to_peer(args.ex_peers.p[lane], static_cast<float>(pg), static_cast<float>(bl),
+                                        static_cast<float>(ent), static_cast<float>(total), args.ex_rank,
+                                        args.ex_world, args.ex_seq);
+            }
+            if (args.ex_world > 0 && args.ex_sums) {
+              __syncwarp();
+              exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world, args.ex_seq,
+                                    args.ex_sums, kExchangeTimeoutNs);
+            }
             if (lane == 0) {
-              const double total = pg + static_cast<double>(a.baseline_cost) * bl +
-                                   static_cast<double>(a.entropy_cost) * ent;
               if (a.losses) {
                 a.losses[0] = static_cast<float>(pg), a.losses[1] = static_cast<float>(bl);
                 a.losses[2] = static_cast<float>(ent), a.losses[3] = static_cast<float>(total);

@@ -13,64 +13,25 @@
 // Y can publish step s+2 only after collecting step s+1, which needs X's
 // publish of s+1, which X's stream orders after its collect of step s.
 #include "common.h"
+#include "exchange.cuh"
 
 namespace vtr {
-
-constexpr int kSlotFloats = VTR_EXCHANGE_SLOT_FLOATS;
-
-struct PeerBuffers {
-  float* p[VTR_EXCHANGE_MAX_RANKS];
-};
 
 __global__ void __launch_bounds__(32) exchange_publish_kernel(const float* __restrict__ values, int n,
                                                               PeerBuffers peers, int rank, int world,
                                                               uint32_t seq) {
   const int r = threadIdx.x;
   if (r >= world) return;
-  float* slot = peers.p[r] + (static_cast<size_t>(seq & 1u) * world + rank) * kSlotFloats;
-  for (int i = 0; i < n; ++i) slot[i] = values[i];
-  __threadfence_system();  // values before the sequence number, system-wide
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(slot + 7)),
-               "r"(seq)
-               : "memory");
+  float v[6];
+  for (int i = 0; i < n; ++i) v[i] = values[i];
+  exchange_publish_to_peer(peers.p[r], v, n, rank, world, seq);
 }
 
 __global__ void __launch_bounds__(32) exchange_collect_kernel(const float* __restrict__ mine, int n,
                                                               int world, uint32_t seq,
                                                               float* __restrict__ sums,
                                                               unsigned long long timeout_ns) {
-  __shared__ int sh_ok[32];
-  const int r = threadIdx.x;
-  const float* base = mine + static_cast<size_t>(seq & 1u) * world * kSlotFloats;
-  int ok = 1;
-  if (r < world) {
-    const uint32_t* flag = reinterpret_cast<const uint32_t*>(base + r * kSlotFloats + 7);
-    unsigned long long t0, now;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (;;) {
-      uint32_t v;
-      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-      if (v == seq) break;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-      if (now - t0 > timeout_ns) {  // a peer never published: do not hang the GPU
-        ok = 0;
-        break;
-      }
-      __nanosleep(100);
-    }
-  }
-  sh_ok[r] = ok;
-  __syncwarp();
-  if (r == 0) {
-    bool all_ok = true;
-    for (int i = 0; i < world; ++i) all_ok = all_ok && sh_ok[i];
-    for (int i = 0; i < n; ++i) {
-      double s = 0.0;  // rank order: the same bits on every rank
-      for (int q = 0; q < world; ++q)
-        s += static_cast<double>(*reinterpret_cast<const volatile float*>(base + q * kSlotFloats + i));
-      sums[i] = all_ok ? static_cast<float>(s) : __int_as_float(0x7fc00000);
-    }
-  }
+  exchange_collect_warp(mine, n, world, seq, sums, timeout_ns);
 }
 
 }  // namespace vtr
@@ -81,6 +42,20 @@ extern "C" size_t vtr_exchange_buffer_bytes(int32_t world) {
   if (world <= 0 || world > VTR_EXCHANGE_MAX_RANKS) return 0;
   return sizeof(float) * 2 * world * VTR_EXCHANGE_SLOT_FLOATS;
 }
+
+namespace vtr {
+int fill_peer_buffers(PeerBuffers* out, void* const* peer_buffers, int world) {
+  if (!peer_buffers) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange: peer_buffers is NULL");
+  if (world <= 0 || world > VTR_EXCHANGE_MAX_RANKS)
+    return fail(VTR_ERR_INVALID_ARGUMENT, "exchange: world must be 1..%d", VTR_EXCHANGE_MAX_RANKS);
+  for (int r = 0; r < VTR_EXCHANGE_MAX_RANKS; ++r) out->p[r] = nullptr;
+  for (int r = 0; r < world; ++r) {
+    if (!peer_buffers[r]) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange: peer %d is NULL", r);
+    out->p[r] = static_cast<float*>(peer_buffers[r]);
+  }
+  return VTR_OK;
+}
+}  // namespace vtr
 
 extern "C" int vtr_exchange_publish_f32(const float* values, int32_t n, void* const* peer_buffers,
                                         int32_t rank, int32_t world, uint32_t seq, void* stream) {
@@ -107,7 +82,7 @@ extern "C" int vtr_exchange_collect_f32(const void* my_buffer, int32_t n, int32_
     return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_exchange_collect: bad world %d", world);
   if (n <= 0 || n > 6) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_exchange_collect: n must be 1..6");
   if (seq == 0) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_exchange_collect: seq must start at 1");
-  const unsigned long long timeout_ns = 2000000000ull;  // 2 s
+  const unsigned long long timeout_ns = vtr::kExchangeTimeoutNs;
   vtr::exchange_collect_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const float*>(my_buffer), n, world, seq, sums, timeout_ns);
   VTR_CUDA_CHECK(cudaGetLastError());

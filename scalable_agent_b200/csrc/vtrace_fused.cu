@@ -182,9 +182,10 @@ static bool sm_tile_preferred(const vtr_fused_params* p) {
 template <int A_CT, bool GRADS>
 static int launch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStream_t stream) {
   if (g_plan.dry_run) {
-    record_plan("fused_sm_tile_kernel<A=%d,%s> grid=%d groups=%d relay=%d ring=%d smem=%zu %s; ", A_CT,
+    record_plan("fused_sm_tile_kernel<A=%d,%s> grid=%d groups=%d relay=%d ring=%d smem=%zu %s%s; ", A_CT,
                 GRADS ? "grads" : "fwd", grid, args.groups, args.relay, args.f.depth, smem,
-                args.cursor ? "speed-weighted tiles, in-kernel final reduction" : "even tiles");
+                args.cursor ? "speed-weighted tiles, in-kernel final reduction" : "even tiles",
+                args.ex_world > 0 ? (args.ex_sums ? " + peer publish + collect" : " + peer publish") : "");
     return VTR_OK;
   }
   auto kernel = fused_sm_tile_kernel<A_CT, GRADS>;
@@ -222,7 +223,8 @@ constexpr int kReductionGroupGranules = 512;
 // Returns VTR_ERR_UNSUPPORTED without launching if the shape does not fit this
 // kernel's shared memory.
 static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* partials,
-                            cudaStream_t stream, int* num_partials, bool* losses_done) {
+                            cudaStream_t stream, int* num_partials, bool* losses_done,
+                            bool* exchange_done) {
   DeviceInfo dev;
   if (int rc = device_info(&dev)) return rc;
   const bool grads = p->d_target_logits != nullptr;
@@ -265,6 +267,15 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
   if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
   *losses_done = balance;
+  // The tile that finishes the reduction also publishes to the peers.
+  args.ex_world = 0, args.ex_rank = 0, args.ex_seq = 0, args.ex_sums = nullptr;
+  for (float*& q : args.ex_peers.p) q = nullptr;
+  if (balance && p->exchange_peer_buffers) {
+    if (int rc = fill_peer_buffers(&args.ex_peers, p->exchange_peer_buffers, p->exchange_world)) return rc;
+    args.ex_world = p->exchange_world, args.ex_rank = p->exchange_rank, args.ex_seq = p->exchange_seq;
+    args.ex_sums = p->exchange_sums;
+    *exchange_done = true;
+  }
 
   // Consumer warps: ~16 per SM.  Two tiles share an SM when the batch needs
   // two or more waves, so that the waves overlap instead of queueing.
@@ -471,6 +482,19 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     if (!vtr::aligned(q, 4)) return fail(VTR_ERR_MISALIGNED, "a float/int32 pointer is not 4-byte aligned");
   if (!vtr::aligned(p->losses_f64, 8)) return fail(VTR_ERR_MISALIGNED, "losses_f64 is not 8-byte aligned");
 
+  const bool want_exchange = p->exchange_peer_buffers != nullptr;
+  if (want_exchange) {
+    if (!p->losses) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_peer_buffers needs `losses`");
+    if (p->exchange_world <= 0 || p->exchange_world > VTR_EXCHANGE_MAX_RANKS || p->exchange_rank < 0 ||
+        p->exchange_rank >= p->exchange_world)
+      return fail(VTR_ERR_INVALID_ARGUMENT, "bad exchange rank/world %d/%d", p->exchange_rank,
+                  p->exchange_world);
+    if (p->exchange_seq == 0) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_seq must start at 1");
+    if (!vtr::aligned(p->exchange_sums, 4)) return fail(VTR_ERR_MISALIGNED, "exchange_sums is not 4-byte aligned");
+    for (int r = 0; r < p->exchange_world; ++r)
+      if (!p->exchange_peer_buffers[r])
+        return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_peer_buffers[%d] is NULL", r);
+  }
   const bool want_losses = p->losses || p->losses_f64;
   double* partials = nullptr;
   if (want_losses) {
@@ -493,12 +517,12 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   if (p->path == VTR_PATH_SM_TILE && !vtr::sm_tile_eligible(p))
     return fail(VTR_ERR_UNSUPPORTED,
                 "VTR_PATH_SM_TILE needs B %% 4 == 0 and 16-byte aligned tensors");
-  bool losses_done = false;
+  bool losses_done = false, exchange_done = false;
   if (want_sm_tile)
     rc = vtr::run_sm_tile_path(p, want_losses ? workspace : nullptr, partials, s, &num_partials,
-                               &losses_done);
+                               &losses_done, &exchange_done);
   if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE) {
-    losses_done = false;
+    losses_done = exchange_done = false;
     if (p->path == VTR_PATH_ITEM || (p->path == VTR_PATH_AUTO && vtr::item_kernel_applies(p)))
       rc = vtr::run_item_path(p, partials, s, &num_partials);
     else
@@ -506,8 +530,21 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   }
   if (rc) return rc;
   if (want_losses && !losses_done) {
-    return vtr_reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
-                             p->losses_f64, stream);
+    rc = vtr_reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
+                           p->losses_f64, stream);
+    if (rc) return rc;
+  }
+  if (want_exchange && !exchange_done) {
+    if (vtr::g_plan.dry_run) {
+      vtr::record_plan("exchange_publish_kernel grid=1; ");
+      if (p->exchange_sums) vtr::record_plan("exchange_collect_kernel grid=1; ");
+      return VTR_OK;
+    }
+    rc = vtr_exchange_publish_f32(p->losses, 4, p->exchange_peer_buffers, p->exchange_rank,
+                                  p->exchange_world, p->exchange_seq, stream);
+    if (rc || !p->exchange_sums) return rc;
+    return vtr_exchange_collect_f32(p->exchange_peer_buffers[p->exchange_rank], 4, p->exchange_world,
+                                    p->exchange_seq, p->exchange_sums, stream);
   }
   return VTR_OK;
 }

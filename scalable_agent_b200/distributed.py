@@ -105,6 +105,40 @@ class LossExchange(object):
     torch.cuda.synchronize(self.device)
     dist.barrier(self.group)   # every buffer is zeroed before anyone publishes
 
+  def attach(self, params, sums=None):
+    """Makes the next fused call do the exchange itself: fills the exchange_*
+    fields of a `_lib.FusedParams` with this exchange's buffers and the next
+    sequence number.  The per-SM kernel then stores the four scalars into the
+    peers from the tile that finishes the loss reduction.  With `sums` (a
+    float32 CUDA tensor of 4) the same tile also waits for the peers' scalars
+    and writes the sum over ranks there, and the step needs no further call;
+    without it follow the fused call with `collect()` on the same stream.
+    Every rank must make the same choice, once per step."""
+    self.seq += 1
+    params.exchange_peer_buffers = ctypes.cast(self._peer_ptrs,
+                                               ctypes.POINTER(ctypes.c_void_p))
+    params.exchange_rank, params.exchange_world = self.rank, self.world
+    params.exchange_seq = self.seq
+    if sums is not None:
+      if (sums.dtype != torch.float32 or sums.numel() < 4 or
+          not sums.is_contiguous() or sums.device != self.device):
+        raise ValueError('sums must be a contiguous float32[4] tensor on %s' % self.device)
+      params.exchange_sums = sums.data_ptr()
+    else:
+      params.exchange_sums = None
+    return self.seq
+
+  def collect(self, n=4):
+    """Sum over ranks of what the ranks published for the current step."""
+    out = torch.empty(n, dtype=torch.float32, device=self.device)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+    with torch.cuda.device(self.device):
+      rc = self.lib.vtr_exchange_collect_f32(
+          self.buffer.data_ptr(), n, self.world, self.seq, out.data_ptr(),
+          stream)
+      self._lib.check(rc, 'vtr_exchange_collect_f32')
+    return out
+
   def all_sum(self, values):
     """values: float32 tensor [n], n <= 6, on this rank's device -> sum over ranks."""
     flat = values.detach().reshape(-1)

@@ -40,8 +40,8 @@ def test_version_and_sizes():
 
 
 def test_struct_layout_matches_header():
-  # 4 ints, 8 pointers, 5 floats + 3 ints, 9 pointers on LP64.
-  assert ctypes.sizeof(_lib.FusedParams) == 16 + 8 * 8 + 32 + 9 * 8
+  # 4 ints, 8 pointers, 5 floats + 3 ints, 9 pointers, 1 pointer + 4 ints + 1 pointer on LP64.
+  assert ctypes.sizeof(_lib.FusedParams) == 16 + 8 * 8 + 32 + 9 * 8 + 8 + 16 + 8
 
 
 def test_argument_errors_are_negative_codes_with_messages():
