@@ -51,11 +51,13 @@ struct SmTileArgs {
   int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
   int num_sm;        // SMs of the device
   int waves;         // tiles per SM (grid = num_sm * waves) when balancing
-  unsigned int* cursor;  // workspace header (zeroed): [0] column cursor, [1] finished
-                         // groups, [16 + k] granules of group k written so far; or null
+  unsigned int* cursor;  // workspace header (zeroed): [0] column cursor and [1] tiles served
+                         // (one 64-bit counter), [2] finished groups, [16 + k] granules
+                         // of group k written so far; or null
   double* group_partials;  // [groups][3], second level of the loss reduction
   int group_gran;          // granules (of 4 columns) per reduction group
   float smoothing;         // weight of the newest measurement in the speed table
+  int share_pct;           // 100; tests shrink every share to force the leftover passes
   // Loss exchange of a sharded batch, done by the tile that finishes the
   // reduction (exchange.cuh); ex_world == 0 turns it off.
   PeerBuffers ex_peers;
@@ -144,16 +146,30 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   // This tile's column range, in granules of 4 columns (16-byte rows).  With a
   // cursor: speed-weighted shares handed out first come, first served.
   // Without: B/4 granules dealt evenly by block index.
-  __shared__ int sh_range[2];
+  //
+  // The weighted shares add up to the batch when every SM runs exactly `waves`
+  // tiles.  Nothing guarantees that (another stream may hold some SMs; with
+  // three or more waves a fast SM takes an extra tile), so the cursor also
+  // counts tiles: the one that draws the last ticket knows that nobody comes
+  // after it and owns whatever is left - up to a full tile in this pass, the
+  // rest in further passes of the loop below.  Too much handed out is harmless:
+  // late tiles find the cursor at B and leave.
+  __shared__ int sh_range[3];  // first column, columns, drew the last ticket
   const int total_gran = B >> 2;
   const unsigned long long t_begin = global_timer_ns();
   if (args.cursor) {
     if (warp == 0) {
-      const int share = weighted_share(args, total_gran, cols >> 2, lane, sm_id());
+      int share = weighted_share(args, total_gran, cols >> 2, lane, sm_id());
+      if (args.share_pct != 100) share = max(1, share * args.share_pct / 100);
       if (lane == 0) {
-        const unsigned int start = atomicAdd(args.cursor, static_cast<unsigned int>(share * 4));
+        const unsigned long long drawn =
+            atomicAdd(reinterpret_cast<unsigned long long*>(args.cursor),
+                      (1ull << 32) | static_cast<unsigned long long>(share * 4));
+        const unsigned int start = static_cast<unsigned int>(drawn & 0xffffffffull);
+        const bool last = static_cast<unsigned int>(drawn >> 32) == gridDim.x - 1;
         sh_range[0] = static_cast<int>(min(start, static_cast<unsigned int>(B)));
-        sh_range[1] = max(0, min(share * 4, B - sh_range[0]));
+        sh_range[1] = max(0, min(last ? cols : share * 4, B - sh_range[0]));
+        sh_range[2] = last;
       }
     }
   } else if (threadIdx.x == 0) {
@@ -161,6 +177,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     const int base = total_gran / G, rem = total_gran % G;
     sh_range[0] = (c * base + min(c, rem)) * 4;
     sh_range[1] = (base + (c < rem ? 1 : 0)) * 4;
+    sh_range[2] = 0;
   }
 
   const int slot_floats = cols * (2 * A + 4);
@@ -173,12 +190,18 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   const uint32_t carry_bars = full_bars + 256u;
   const uint32_t ring_u32 = ptx::smem_u32(ring);
 
+  int cols_done = 0;
+  for (int pass = 0;; ++pass) {  // one pass, except for the last ticket's leftovers
   if (threadIdx.x == 0) {
     for (int s = 0; s < depth; ++s) {
+      if (pass > 0) ptx::mbar_inval(full_bars + 8u * s), ptx::mbar_inval(empty_bars + 8u * s);
       ptx::mbar_init(full_bars + 8u * s, 1);
       ptx::mbar_init(empty_bars + 8u * s, NG);
     }
-    for (int w = 0; w < consumers; ++w) ptx::mbar_init(carry_bars + 8u * w, 32);
+    for (int w = 0; w < consumers; ++w) {
+      if (pass > 0) ptx::mbar_inval(carry_bars + 8u * w);
+      ptx::mbar_init(carry_bars + 8u * w, 32);
+    }
     ptx::fence_mbar_init();
     ptx::fence_proxy_async();
   }
@@ -421,7 +444,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
             double* out = args.group_partials + 3 * grp;
             out[0] = g0, out[1] = g1, out[2] = g2;
             __threadfence();
-            sh_flag = atomicAdd(args.cursor + 1, 1u) == static_cast<unsigned int>(num_groups - 1);
+            sh_flag = atomicAdd(args.cursor + 2, 1u) == static_cast<unsigned int>(num_groups - 1);
           }
           __syncwarp();
           if (sh_flag) {  // every group is complete: the final sum, in group order
@@ -457,12 +480,20 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
       __syncthreads();
     }
   }
-  if (threadIdx.x == 0 && ncols > 0) {
+  cols_done += ncols;
+  if (!sh_range[2] || col0 + ncols >= B) break;
+  __syncthreads();  // everybody is done with this pass's range and barriers
+  if (threadIdx.x == 0) {
+    sh_range[0] = col0 + ncols;
+    sh_range[1] = min(cols, B - (col0 + ncols));
+  }
+  }  // pass
+  if (threadIdx.x == 0 && cols_done > 0) {
     const unsigned int sm = sm_id();
     const unsigned long long dt = global_timer_ns() - t_begin;
     // Tiles shorter than 20 us measure launch latency, not the SM: leave the table alone.
     if (sm < kMaxSms && dt > 20000) {
-      const float speed = static_cast<float>(ncols) * T / static_cast<float>(dt);
+      const float speed = static_cast<float>(cols_done) * T / static_cast<float>(dt);
       const float old = g_sm_speed[sm];
       g_sm_speed[sm] = old > 0.0f ? old + args.smoothing * (speed - old) : speed;
     }

@@ -265,6 +265,8 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
     args.group_gran = (total_gran + kMaxReductionGroups - 1) / kMaxReductionGroups;
   args.smoothing = 0.5f;
   if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
+  args.share_pct = 100;
+  if (const int pct = env_int("VTR_SM_SHARE_PCT")) args.share_pct = min(100, max(1, pct));  // tests only
   if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
   *losses_done = balance;
   // The tile that finishes the reduction also publishes to the peers.

@@ -211,6 +211,24 @@ def test_fused_matches_oracle(api, T, B, A, path):
   _check_fused(experiment, inp, path=path)
 
 
+@pytest.mark.parametrize('share_pct', [60, 93])
+@pytest.mark.parametrize('T,B,A', [(12, 148 * 64, 6), (6, 70000, 3), (40, 148 * 160, 18)])
+def test_sm_tile_kernel_covers_the_batch_when_shares_fall_short(api, monkeypatch, T, B, A,
+                                                                 share_pct):
+  """K1c sizes tiles from per-SM speeds on the assumption that every SM runs
+  the same number of tiles; when that does not hold the shares need not add
+  up to B.  Shrinking every share (test knob) forces it: the tile that draws
+  the last ticket must pick up every column nobody was given."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T + B + A)
+  # the shrunk call comes first: a column it skipped shows whatever the
+  # allocator left there, not an earlier identical call's correct value
+  monkeypatch.setenv('VTR_SM_SHARE_PCT', str(share_pct))
+  _check_fused(experiment, inp, path='sm_tile')
+  monkeypatch.delenv('VTR_SM_SHARE_PCT')
+  _check_fused(experiment, inp, path='sm_tile')
+
+
 @pytest.mark.parametrize('T,B,A', [
     (5, 4, 3), (100, 32, 9), (20, 512, 18), (1, 4, 1), (2, 8, 4), (3, 64, 6),
     (7, 68, 5), (40, 36, 7), (9, 100, 32), (6, 36, 100), (4, 4, 256),
