@@ -276,6 +276,48 @@ int vtr_exchange_publish_f32(const float* values, int32_t n, void* const* peer_b
 int vtr_exchange_collect_f32(const void* my_buffer, int32_t n, int32_t world, uint32_t seq,
                              float* sums, void* stream);
 
+/*
+ * The optimiser step that follows the path: experiment.py:410-415,
+ *   learning_rate = tf.train.polynomial_decay(lr, num_env_frames, total_frames, 0)
+ *   tf.train.RMSPropOptimizer(learning_rate, decay, momentum, epsilon).minimize(total_loss)
+ * with TensorFlow 1.9.0's ApplyRMSProp:
+ *   ms <- ms + (1 - decay)(g^2 - ms);  mom <- momentum mom + lr g / sqrt(ms + epsilon);  var <- var - mom.
+ * The slots start as tf.train.RMSPropOptimizer creates them: ms = 1, mom = 0
+ * (the caller initialises them).  All buffers float32, 16-byte aligned.
+ */
+/* experiment.py:411-412 (cycle=False); plain host arithmetic in double. */
+double vtr_polynomial_decay(double learning_rate, int64_t global_step, int64_t decay_steps,
+                            double end_learning_rate, double power);
+/* experiment.py:413-415 on one GPU, in place.  `mom` may be NULL when momentum
+   == 0 (the reference's default, experiment.py:94): the slot would only ever
+   hold the last update. */
+int vtr_rmsprop_f32(float* var, float* ms, float* mom, const float* grad, int64_t n,
+                    float learning_rate, float decay, float momentum, float epsilon, void* stream);
+/*
+ * The same step for a learner whose batch is sharded over the GPUs of one box
+ * (no counterpart in the reference, which has a single learner,
+ * experiment.py:491): the gradient is the sum of the ranks' gradients.  One
+ * launch per rank does reduce-scatter, update and all-gather over NVLink peer
+ * memory.  Every rank owns three buffers its peers can access (e.g. torch
+ * symmetric memory): the full parameters [n], its full local gradient [n], and
+ * vtr_rmsprop_sync_bytes() of zero-initialised sync words; `*_peers` are HOST
+ * arrays of the `world` device pointers to them as mapped on this rank, own
+ * included.  The slots are sharded: rank r holds only ms/mom of its slice
+ * [lo, hi) of the parameters (vtr_rmsprop_slice; element 0 of `ms_slice` is
+ * parameter lo).  Call once per step on every rank with the same n, seq = 1,
+ * 2, 3, ... and hyper-parameters; when the call has completed on a rank, that
+ * rank's parameter buffer holds the updated values of all slices and its
+ * gradient buffer may be overwritten.  Gradients are summed in rank order, so
+ * all ranks hold the same bits.  A peer that does not show up within 2 s sets
+ * word 33 of this rank's sync buffer to 1 instead of hanging the GPU.
+ */
+int vtr_rmsprop_slice(int64_t n, int32_t world, int32_t rank, int64_t* lo, int64_t* hi);
+size_t vtr_rmsprop_sync_bytes(void);
+int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* grad_peers, void* const* sync_peers,
+                              float* ms_slice, float* mom_slice, int64_t n, int32_t rank, int32_t world,
+                              uint32_t seq, float learning_rate, float decay, float momentum,
+                              float epsilon, void* stream);
+
 /* x[i] *= *scale for i < n, skipped entirely when *scale == 1.  `scale` is a
    device float[1].  Used to apply the upstream gradient of the total loss
    (experiment.py:415) to the gradients the fused pass already produced,

@@ -98,6 +98,16 @@ SIGNATURES = {
     'vtr_exchange_publish_f32':
         (ctypes.c_int, [_P, _I32, ctypes.POINTER(ctypes.c_void_p), _I32, _I32, _U32, _P]),
     'vtr_exchange_collect_f32': (ctypes.c_int, [_P, _I32, _I32, _U32, _P, _P]),
+    'vtr_polynomial_decay':
+        (ctypes.c_double, [ctypes.c_double, _I64, _I64, ctypes.c_double, ctypes.c_double]),
+    'vtr_rmsprop_f32': (ctypes.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _P]),
+    'vtr_rmsprop_slice':
+        (ctypes.c_int, [_I64, _I32, _I32, ctypes.POINTER(_I64), ctypes.POINTER(_I64)]),
+    'vtr_rmsprop_sync_bytes': (_SZ, []),
+    'vtr_rmsprop_allreduce_f32':
+        (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
+                        ctypes.POINTER(ctypes.c_void_p), _P, _P, _I64, _I32, _I32, _U32,
+                        _F, _F, _F, _F, _P]),
 }
 
 _lib = None
