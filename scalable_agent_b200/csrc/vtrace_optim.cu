@@ -124,8 +124,13 @@ __device__ __forceinline__ float4 add4(const float4& a, const float4& b) {
   return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w));
 }
 
-template <bool HAS_MOM>
+// U float4 groups per thread and iteration, their loads from 8 / U ranks at a
+// time: always eight 16-byte loads in flight per thread.  NVLink loads take a
+// few microseconds to come back, so with one or two peers a thread has to
+// cover several groups at once to keep the links busy.
+template <bool HAS_MOM, int U>
 __global__ void __launch_bounds__(256) rmsprop_allreduce_kernel(const __grid_constant__ RmsShardArgs a) {
+  constexpr int RC = 8 / U;
   __shared__ int sh_ok, sh_last;
   uint32_t* my_sync = reinterpret_cast<uint32_t*>(a.sync.p[a.rank]);
   const int tid = threadIdx.x;
@@ -149,29 +154,36 @@ __global__ void __launch_bounds__(256) rmsprop_allreduce_kernel(const __grid_con
     const long stride = static_cast<long>(gridDim.x) * blockDim.x;
     float4* ms4 = reinterpret_cast<float4*>(a.ms);
     float4* mom4 = reinterpret_cast<float4*>(a.mom);
-    for (long i = static_cast<long>(blockIdx.x) * blockDim.x + tid; i < groups; i += stride) {
-      const long e = a.lo + (i << 2);
-      // Eight ranks at a time: their loads are all in flight before the first
-      // add; the adds run in rank order.
-      float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-      for (int r0 = 0; r0 < a.world; r0 += 8) {
-        float4 part[8];
+    for (long i0 = static_cast<long>(blockIdx.x) * blockDim.x + tid; i0 < groups; i0 += stride * U) {
+      float4 g[U];
+      for (int r0 = 0; r0 < a.world; r0 += RC) {
+        float4 part[U][RC];
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (r0 + k < a.world) part[k] = __ldcg(reinterpret_cast<const float4*>(a.grad.p[r0 + k] + e));
+        for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (r0 + k < a.world) g = (r0 + k == 0) ? part[0] : add4(g, part[k]);
+          for (int k = 0; k < RC; ++k)
+            if (r0 + k < a.world && i0 + u * stride < groups)
+              part[u][k] = __ldcg(reinterpret_cast<const float4*>(a.grad.p[r0 + k] + a.lo +
+                                                                  ((i0 + u * stride) << 2)));
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int k = 0; k < RC; ++k)  // rank order
+            if (r0 + k < a.world) g[u] = (r0 + k == 0) ? part[u][0] : add4(g[u], part[u][k]);
       }
-      float4 v = __ldcg(reinterpret_cast<const float4*>(a.var.p[a.rank] + e));
-      float4 m = ms4[i];
-      float4 mo = HAS_MOM ? mom4[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-      rms_update4(v, m, mo, g, a.h);
-      ms4[i] = m;
-      if (HAS_MOM) mom4[i] = mo;
 #pragma unroll
-      for (int r = 0; r < VTR_EXCHANGE_MAX_RANKS; ++r)
-        if (r < a.world) *reinterpret_cast<float4*>(a.var.p[r] + e) = v;
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i >= groups) break;
+        const long e = a.lo + (i << 2);
+        float4 v = __ldcg(reinterpret_cast<const float4*>(a.var.p[a.rank] + e));
+        float4 m = ms4[i];
+        float4 mo = HAS_MOM ? mom4[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        rms_update4(v, m, mo, g[u], a.h);
+        ms4[i] = m;
+        if (HAS_MOM) mom4[i] = mo;
+        for (int r = 0; r < a.world; ++r) *reinterpret_cast<float4*>(a.var.p[r] + e) = v;
+      }
     }
     // the last, partial group of the whole buffer belongs to whoever owns it
     const long e = a.lo + (groups << 2) + tid;
@@ -303,10 +315,20 @@ extern "C" int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* gr
   a.h = {learning_rate, 1.0f - decay, momentum, epsilon};
   a.timeout_ns = vtr::kExchangeTimeoutNs;
   // Every rank launches, even one whose slice is empty: its peers wait for its flags.
-  const int blocks = blocks_for((hi - lo) >> 2);
+  const int unroll = world <= 2 ? 4 : world <= 4 ? 2 : 1;
+  const int blocks = blocks_for((((hi - lo) >> 2) + unroll - 1) / unroll);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (mom_slice) vtr::rmsprop_allreduce_kernel<true><<<blocks, 256, 0, s>>>(a);
-  else vtr::rmsprop_allreduce_kernel<false><<<blocks, 256, 0, s>>>(a);
+  const bool m = mom_slice != nullptr;
+  if (unroll == 4) {
+    if (m) vtr::rmsprop_allreduce_kernel<true, 4><<<blocks, 256, 0, s>>>(a);
+    else vtr::rmsprop_allreduce_kernel<false, 4><<<blocks, 256, 0, s>>>(a);
+  } else if (unroll == 2) {
+    if (m) vtr::rmsprop_allreduce_kernel<true, 2><<<blocks, 256, 0, s>>>(a);
+    else vtr::rmsprop_allreduce_kernel<false, 2><<<blocks, 256, 0, s>>>(a);
+  } else {
+    if (m) vtr::rmsprop_allreduce_kernel<true, 1><<<blocks, 256, 0, s>>>(a);
+    else vtr::rmsprop_allreduce_kernel<false, 1><<<blocks, 256, 0, s>>>(a);
+  }
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;
 }
