@@ -106,11 +106,13 @@ def main():
       params[0].grad.normal_()
       us = max_over_ranks(timed(opt.step, args.steps, args.warmup, barrier))
       opt.check_peers()
-      per_rank = (opt.hi - opt.lo) * 4
+      # into a rank: what it loads from its N-1 peers (their part of the sum for
+      # its slice) plus what the N-1 peers store into its parameters (their
+      # slices); out of it: the mirror image
+      per_direction = 2 * (opt.hi - opt.lo) * 4 * (world - 1)
       lines.append({'impl': 'fused', 'n_gpus': world, 'params': n, 'us_per_step': us,
-                    'nvlink_bytes_in_per_rank': per_rank * (world - 1),
-                    'nvlink_bytes_out_per_rank': per_rank * (world - 1),
-                    'nvlink_gbs_per_direction': per_rank * (world - 1) / us * 1e-3})
+                    'nvlink_bytes_per_direction_per_rank': per_direction,
+                    'nvlink_gbs_per_direction': per_direction / us * 1e-3})
       del opt, params
       var = torch.randn(n, device=device)
       ms = torch.ones(n, device=device)
