@@ -57,7 +57,7 @@ def main():
     shapes.append(('extra_%s' % spec, T, B, A))
   with open(args.out, 'w') as f:
     for name, T, B, A in shapes:
-      if args.only and args.only not in name:
+      if args.only and not any(tag in name for tag in args.only.split(',')):
         continue
       inp = bench.synthetic_on_device(T, B, A, 1, device)
       for path in args.paths.split(','):

@@ -1,5 +1,6 @@
 // Version, error reporting and device-property cache of libvtrace_b200.so.
 #include <mutex>
+#include <unordered_map>
 
 #include "common.h"
 
@@ -44,6 +45,26 @@ int device_info(DeviceInfo* out) {
     valid[dev] = true;
   }
   *out = cache[dev];
+  return VTR_OK;
+}
+
+// cudaFuncSetAttribute costs microseconds of host time on every call; the
+// opt-in only ever has to grow, so remember what each kernel already has on
+// each device.
+int allow_dynamic_smem(const void* kernel, size_t bytes) {
+  static std::unordered_map<unsigned long long, size_t> granted;
+  static std::mutex mu;
+  int dev = 0;
+  VTR_CUDA_CHECK(cudaGetDevice(&dev));
+  const unsigned long long key =
+      (static_cast<unsigned long long>(reinterpret_cast<uintptr_t>(kernel)) << 8) ^
+      static_cast<unsigned>(dev & 0xff);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = granted.find(key);
+  if (it != granted.end() && it->second >= bytes) return VTR_OK;
+  VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(bytes)));
+  granted[key] = bytes;
   return VTR_OK;
 }
 

@@ -29,6 +29,10 @@ struct DeviceInfo {
 // Queries (and caches per device) the properties the launch heuristics use.
 int device_info(DeviceInfo* out);
 
+// Raises a kernel's dynamic shared memory opt-in to `bytes` on the current
+// device if it is not already that high (cached: no driver call once granted).
+int allow_dynamic_smem(const void* kernel, size_t bytes);
+
 constexpr float kLog2e = 1.4426950408889634f;
 
 }  // namespace vtr

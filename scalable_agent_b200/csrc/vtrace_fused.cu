@@ -100,8 +100,7 @@ static int launch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem
     return VTR_OK;
   }
   auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
-  VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(smem)));
+  if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
   kernel<<<tiles, 32 * warps, smem, stream>>>(args);
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;
@@ -189,8 +188,7 @@ static int launch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStr
     return VTR_OK;
   }
   auto kernel = fused_sm_tile_kernel<A_CT, GRADS>;
-  VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(smem)));
+  if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
   kernel<<<grid, 32 * (args.groups * args.relay + 1), smem, stream>>>(args);
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;

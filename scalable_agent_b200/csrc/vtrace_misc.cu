@@ -241,8 +241,7 @@ static int launch_rows(RowArgs a, cudaStream_t stream) {
   a.stride = a.A | 1;
   const size_t smem = static_cast<size_t>(R) * a.stride * sizeof(float);
   auto kernel = row_kernel<MODE>;
-  VTR_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(smem)));
+  if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
   const long blocks = row_blocks(a.rows, a.A);
   if (blocks > 0x7fffffffL) return fail(VTR_ERR_UNSUPPORTED, "too many rows (%ld)", a.rows);
   kernel<<<static_cast<unsigned>(blocks), R, smem, stream>>>(a);
