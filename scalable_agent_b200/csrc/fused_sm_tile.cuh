@@ -43,6 +43,7 @@ constexpr int kMaxSms = 256;
 // idle for the last quarter of the kernel.  Only the partition depends on
 // this table; every output value is independent of the partition.
 static __device__ float g_sm_speed[kMaxSms];
+static __device__ unsigned int g_sm_samples[kMaxSms];  // measurements behind each entry
 
 struct SmTileArgs {
   FusedArgs f;
@@ -56,7 +57,7 @@ struct SmTileArgs {
                          // of group k written so far; or null
   double* group_partials;  // [groups][3], second level of the loss reduction
   int group_gran;          // granules (of 4 columns) per reduction group
-  float smoothing;         // weight of the newest measurement in the speed table
+  float smoothing;         // least weight of the newest measurement in the speed table
   int share_pct;           // 100; tests shrink every share to force the leftover passes
   // Loss exchange of a sharded batch, done by the tile that finishes the
   // reduction (exchange.cuh); ex_world == 0 turns it off.
@@ -494,8 +495,14 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     // Tiles shorter than 20 us measure launch latency, not the SM: leave the table alone.
     if (sm < kMaxSms && dt > 20000) {
       const float speed = static_cast<float>(cols_done) * T / static_cast<float>(dt);
+      // Running mean over the first 1 / smoothing measurements, exponential
+      // after: one tile's time is noisy (+-2 % from call to call on the same
+      // addresses), and noise in the table is imbalance in the next call.
+      const unsigned int n = g_sm_samples[sm] + 1u;
+      const float weight = fmaxf(args.smoothing, 1.0f / static_cast<float>(n));
       const float old = g_sm_speed[sm];
-      g_sm_speed[sm] = old > 0.0f ? old + args.smoothing * (speed - old) : speed;
+      g_sm_speed[sm] = old > 0.0f ? old + weight * (speed - old) : speed;
+      if (n < 1000000u) g_sm_samples[sm] = n;
     }
   }
 }

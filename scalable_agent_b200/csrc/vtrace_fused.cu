@@ -261,7 +261,7 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   args.group_gran = kReductionGroupGranules;
   if ((total_gran + args.group_gran - 1) / args.group_gran > kMaxReductionGroups)
     args.group_gran = (total_gran + kMaxReductionGroups - 1) / kMaxReductionGroups;
-  args.smoothing = 0.5f;
+  args.smoothing = 0.05f;
   if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
   args.share_pct = 100;
   if (const int pct = env_int("VTR_SM_SHARE_PCT")) args.share_pct = min(100, max(1, pct));  // tests only
