@@ -96,11 +96,6 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
-// ---- streaming global access ------------------------------------------------
-__device__ __forceinline__ void st_cs(float* p, float v) {
-  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
-}
-
 // ---- MUFU approximations ----------------------------------------------------
 __device__ __forceinline__ float ex2(float x) {
   float y;
