@@ -14,16 +14,51 @@ from scalable_agent_b200 import _lib
 _NS = 'b200vtrace'
 
 
+_cuda_ok = False
+
+
 def require_cuda():
+  global _cuda_ok
+  if _cuda_ok:              # asked once: the answer does not change while we run
+    return
   if not torch.cuda.is_available():
     raise RuntimeError(
         'scalable_agent_b200 needs a CUDA device (B200, sm_100a); '
         'there is no CPU fallback.')
   _lib.load()
+  _cuda_ok = True
 
 
 def _stream(device):
+  """The current stream of `device` as the void* the C ABI takes."""
+  raw = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+  if raw is not None:       # same stream, without building a torch.cuda.Stream
+    return ctypes.c_void_p(raw(device.index if device.index is not None
+                               else torch.cuda.current_device()))
   return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+# Every kernel entry point below is registered as a torch custom op (so that
+# torch.compile / export see an opaque, shape-annotated op), but a call through
+# the dispatcher costs 50-100 us of host time - more than most of the kernels
+# take.  The autograd wrappers and the API therefore call the op's own Python
+# body directly in eager mode and the registered op only while compiling.
+_BODY = {}
+
+
+def _custom_op(name, mutates_args=()):
+  def register(fn):
+    op = torch.library.custom_op(_NS + '::' + name, mutates_args=mutates_args)(fn)
+    _BODY[op] = fn
+    return op
+  return register
+
+
+def call(op, *args):
+  """`op(*args)`; in eager mode without the trip through the dispatcher."""
+  if torch.compiler.is_compiling():
+    return op(*args)
+  return _BODY[op](*args)
 
 
 def _ptr(t):
@@ -49,7 +84,7 @@ def _check_cuda(*tensors):
 # ---------------------------------------------------------------------------
 # Fused V-trace + losses + gradients (vtr_from_logits_fused_f32)
 # ---------------------------------------------------------------------------
-@torch.library.custom_op(_NS + '::from_logits_fused', mutates_args=())
+@_custom_op('from_logits_fused')
 def from_logits_fused(
     behaviour_policy_logits: torch.Tensor, target_policy_logits: torch.Tensor,
     actions: torch.Tensor, discounts: torch.Tensor, rewards: torch.Tensor,
@@ -145,7 +180,7 @@ def _(behaviour_policy_logits, target_policy_logits, actions, discounts,
 # ---------------------------------------------------------------------------
 # Stand-alone pieces
 # ---------------------------------------------------------------------------
-@torch.library.custom_op(_NS + '::from_importance_weights', mutates_args=())
+@_custom_op('from_importance_weights')
 def from_importance_weights(
     log_rhos: torch.Tensor, discounts: torch.Tensor, rewards: torch.Tensor,
     values: torch.Tensor, bootstrap_value: torch.Tensor, C: int,
@@ -177,7 +212,7 @@ def _(log_rhos, discounts, rewards, values, bootstrap_value, C, bcast_mask,
   return torch.empty_like(values), torch.empty_like(values)
 
 
-@torch.library.custom_op(_NS + '::log_probs', mutates_args=())
+@_custom_op('log_probs')
 def log_probs(policy_logits: torch.Tensor, actions: torch.Tensor) -> torch.Tensor:
   require_cuda()
   dev = _check_cuda(policy_logits, actions)
@@ -201,7 +236,7 @@ def _loss_workspace(units, dev):
   return torch.empty(nbytes // 8, dtype=torch.float64, device=dev), nbytes
 
 
-@torch.library.custom_op(_NS + '::pg_loss', mutates_args=())
+@_custom_op('pg_loss')
 def pg_loss(logits: torch.Tensor, actions: torch.Tensor,
             advantages: torch.Tensor) -> torch.Tensor:
   require_cuda()
@@ -223,7 +258,7 @@ def _(logits, actions, advantages):
   return logits.new_empty(())
 
 
-@torch.library.custom_op(_NS + '::pg_loss_bwd', mutates_args=())
+@_custom_op('pg_loss_bwd')
 def pg_loss_bwd(logits: torch.Tensor, actions: torch.Tensor,
                 advantages: torch.Tensor, grad_out: torch.Tensor) -> torch.Tensor:
   require_cuda()
@@ -243,7 +278,7 @@ def _(logits, actions, advantages, grad_out):
   return torch.empty_like(logits)
 
 
-@torch.library.custom_op(_NS + '::entropy_loss', mutates_args=())
+@_custom_op('entropy_loss')
 def entropy_loss(logits: torch.Tensor) -> torch.Tensor:
   require_cuda()
   dev = _check_cuda(logits)
@@ -263,7 +298,7 @@ def _(logits):
   return logits.new_empty(())
 
 
-@torch.library.custom_op(_NS + '::entropy_loss_bwd', mutates_args=())
+@_custom_op('entropy_loss_bwd')
 def entropy_loss_bwd(logits: torch.Tensor, grad_out: torch.Tensor) -> torch.Tensor:
   require_cuda()
   dev = _check_cuda(logits, grad_out)
@@ -282,7 +317,7 @@ def _(logits, grad_out):
   return torch.empty_like(logits)
 
 
-@torch.library.custom_op(_NS + '::baseline_loss', mutates_args=())
+@_custom_op('baseline_loss')
 def baseline_loss(advantages: torch.Tensor) -> torch.Tensor:
   require_cuda()
   dev = _check_cuda(advantages)
@@ -301,7 +336,7 @@ def _(advantages):
   return advantages.new_empty(())
 
 
-@torch.library.custom_op(_NS + '::baseline_loss_bwd', mutates_args=())
+@_custom_op('baseline_loss_bwd')
 def baseline_loss_bwd(advantages: torch.Tensor,
                       grad_out: torch.Tensor) -> torch.Tensor:
   require_cuda()
@@ -320,7 +355,7 @@ def _(advantages, grad_out):
   return torch.empty_like(advantages)
 
 
-@torch.library.custom_op(_NS + '::scale_inplace', mutates_args=('x',))
+@_custom_op('scale_inplace', mutates_args=('x',))
 def scale_inplace(x: torch.Tensor, scale: torch.Tensor) -> None:
   """x *= scale (device scalar), a no-op launch when scale == 1."""
   require_cuda()
@@ -345,7 +380,7 @@ class LogProbs(torch.autograd.Function):
   @staticmethod
   def forward(ctx, policy_logits, actions):
     ctx.save_for_backward(policy_logits, actions)
-    return log_probs(policy_logits, actions)
+    return call(log_probs, policy_logits, actions)
 
   @staticmethod
   @torch.autograd.function.once_differentiable
@@ -353,7 +388,7 @@ class LogProbs(torch.autograd.Function):
     policy_logits, actions = ctx.saved_tensors
     one = torch.ones(1, dtype=torch.float32, device=g.device)
     # d(sum g*lp) = -(d sum CE*g): reuse the policy-gradient backward kernel.
-    return pg_loss_bwd(policy_logits, actions, (-g).contiguous(), one), None
+    return call(pg_loss_bwd, policy_logits, actions, (-g).contiguous(), one), None
 
 
 class PolicyGradientLoss(torch.autograd.Function):
@@ -361,14 +396,14 @@ class PolicyGradientLoss(torch.autograd.Function):
   @staticmethod
   def forward(ctx, logits, actions, advantages):
     ctx.save_for_backward(logits, actions, advantages)
-    return pg_loss(logits, actions, advantages)
+    return call(pg_loss, logits, actions, advantages)
 
   @staticmethod
   @torch.autograd.function.once_differentiable
   def backward(ctx, g):
     logits, actions, advantages = ctx.saved_tensors
     # advantages are stop_gradient in the reference (experiment.py:341).
-    return pg_loss_bwd(logits, actions, advantages, _scalar_f32(g)), None, None
+    return call(pg_loss_bwd, logits, actions, advantages, _scalar_f32(g)), None, None
 
 
 class EntropyLoss(torch.autograd.Function):
@@ -376,13 +411,13 @@ class EntropyLoss(torch.autograd.Function):
   @staticmethod
   def forward(ctx, logits):
     ctx.save_for_backward(logits)
-    return entropy_loss(logits)
+    return call(entropy_loss, logits)
 
   @staticmethod
   @torch.autograd.function.once_differentiable
   def backward(ctx, g):
     (logits,) = ctx.saved_tensors
-    return entropy_loss_bwd(logits, _scalar_f32(g))
+    return call(entropy_loss_bwd, logits, _scalar_f32(g))
 
 
 class BaselineLoss(torch.autograd.Function):
@@ -390,13 +425,13 @@ class BaselineLoss(torch.autograd.Function):
   @staticmethod
   def forward(ctx, advantages):
     ctx.save_for_backward(advantages)
-    return baseline_loss(advantages)
+    return call(baseline_loss, advantages)
 
   @staticmethod
   @torch.autograd.function.once_differentiable
   def backward(ctx, g):
     (advantages,) = ctx.saved_tensors
-    return baseline_loss_bwd(advantages, _scalar_f32(g))
+    return call(baseline_loss_bwd, advantages, _scalar_f32(g))
 
 
 class FromLogits(torch.autograd.Function):
@@ -408,7 +443,8 @@ class FromLogits(torch.autograd.Function):
   def forward(ctx, behaviour_policy_logits, target_policy_logits, actions,
               discounts, rewards, values, bootstrap_value, clip_rho_threshold,
               clip_pg_rho_threshold, path):
-    vs, pg, log_rhos, b_lp, t_lp, _, _, _ = from_logits_fused(
+    vs, pg, log_rhos, b_lp, t_lp, _, _, _ = call(
+        from_logits_fused,
         behaviour_policy_logits, target_policy_logits, actions, discounts,
         rewards, values, bootstrap_value, None, clip_rho_threshold,
         clip_pg_rho_threshold, 0.0, 0.0, 0.0, 0, True, False, False, path)
@@ -423,10 +459,10 @@ class FromLogits(torch.autograd.Function):
     one = torch.ones(1, dtype=torch.float32, device=target.device)
     d_behaviour = d_target = None
     if ctx.needs_input_grad[0]:
-      d_behaviour = pg_loss_bwd(behaviour, actions,
+      d_behaviour = call(pg_loss_bwd, behaviour, actions,
                                 (g_log_rhos - g_b_lp).contiguous(), one)
     if ctx.needs_input_grad[1]:
-      d_target = pg_loss_bwd(target, actions,
+      d_target = call(pg_loss_bwd, target, actions,
                              (-(g_log_rhos + g_t_lp)).contiguous(), one)
     return (d_behaviour, d_target) + (None,) * 8
 
@@ -445,7 +481,8 @@ class FusedLoss(torch.autograd.Function):
               clip_rho_threshold, clip_pg_rho_threshold, baseline_cost,
               entropy_cost, discounting, reward_clip_mode, want_aux, path):
     want_grads = ctx.needs_input_grad[1] or ctx.needs_input_grad[5]
-    vs, pg, log_rhos, b_lp, t_lp, losses, d_logits, d_values = from_logits_fused(
+    vs, pg, log_rhos, b_lp, t_lp, losses, d_logits, d_values = call(
+        from_logits_fused,
         behaviour_policy_logits, target_policy_logits, actions, discounts,
         rewards, values, bootstrap_value, done, clip_rho_threshold,
         clip_pg_rho_threshold, baseline_cost, entropy_cost, discounting,
@@ -465,8 +502,8 @@ class FusedLoss(torch.autograd.Function):
     ctx.backward_ran = True
     d_logits, d_values = ctx.saved_tensors
     g = _scalar_f32(g_total)
-    scale_inplace(d_logits, g)
-    scale_inplace(d_values, g)
+    call(scale_inplace, d_logits, g)
+    call(scale_inplace, d_values, g)
     grads = [None] * 16
     if ctx.needs_input_grad[1]:
       grads[1] = d_logits
@@ -492,7 +529,8 @@ class FusedLearnerLoss(torch.autograd.Function):
     T = learner_logits.shape[0] - 1
     want_grads = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
     empty = torch.empty(0, dtype=torch.float32, device=learner_logits.device)
-    vs, pg, log_rhos, b_lp, t_lp, losses, d_logits, d_values = from_logits_fused(
+    vs, pg, log_rhos, b_lp, t_lp, losses, d_logits, d_values = call(
+        from_logits_fused,
         behaviour_logits[1:], learner_logits[:T], actions[1:], empty,
         rewards[1:], learner_baseline[:T], learner_baseline[T], done[1:],
         clip_rho_threshold, clip_pg_rho_threshold, baseline_cost, entropy_cost,
@@ -512,8 +550,8 @@ class FusedLearnerLoss(torch.autograd.Function):
     ctx.backward_ran = True
     d_logits, d_values = ctx.saved_tensors
     g = _scalar_f32(g_total)
-    scale_inplace(d_logits, g)
-    scale_inplace(d_values, g)
+    call(scale_inplace, d_logits, g)
+    call(scale_inplace, d_values, g)
     grads = [None] * 14
     if ctx.needs_input_grad[0]:
       grads[0] = d_logits

@@ -198,7 +198,8 @@ def from_importance_weights(
   bootstrap_value = widen(bootstrap_value, (B,))
 
   with torch.no_grad():
-    vs, pg = _ops.from_importance_weights(
+    vs, pg = _ops.call(
+        _ops.from_importance_weights,
         log_rhos.detach(), discounts.detach(), rewards.detach(),
         values.detach().reshape(T, B, C), bootstrap_value.detach(), C,
         bcast_mask, clip_rho_threshold, clip_pg_rho_threshold)
