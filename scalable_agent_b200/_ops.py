@@ -61,6 +61,25 @@ def call(op, *args):
   return _BODY[op](*args)
 
 
+class _NoSwitch(object):
+  def __enter__(self):
+    return None
+
+  def __exit__(self, *exc):
+    return False
+
+
+_NO_SWITCH = _NoSwitch()
+
+
+def _on(device):
+  """Context that makes `device` current for the launch; nothing to do - and
+  nothing spent - when it already is."""
+  if device.index is None or device.index == torch.cuda.current_device():
+    return _NO_SWITCH
+  return torch.cuda.device(device)
+
+
 def _ptr(t):
   return ctypes.c_void_p(t.data_ptr()) if t is not None else None
 
@@ -154,7 +173,7 @@ def from_logits_fused(
     p.losses = losses.data_ptr()
     ws_bytes = lib.vtr_fused_workspace_bytes(T, B, A)
     workspace = torch.empty(ws_bytes // 8, dtype=torch.float64, device=dev)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = lib.vtr_from_logits_fused_f32(
         ctypes.byref(p), _ptr(workspace), ws_bytes, _stream(dev))
   _lib.check(rc, 'vtr_from_logits_fused_f32')
@@ -195,7 +214,7 @@ def from_importance_weights(
   pg = torch.empty_like(values)
   flags = ((_lib.FLAG_NO_CLIP_RHO if clip_rho_threshold is None else 0) |
            (_lib.FLAG_NO_CLIP_PG_RHO if clip_pg_rho_threshold is None else 0))
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_from_importance_weights_f32(
         _ptr(log_rhos), _ptr(discounts), _ptr(rewards), _ptr(values),
         _ptr(bootstrap_value), T, B, C, bcast_mask,
@@ -219,7 +238,7 @@ def log_probs(policy_logits: torch.Tensor, actions: torch.Tensor) -> torch.Tenso
   A = policy_logits.shape[-1]
   rows = policy_logits.numel() // A
   out = torch.empty(policy_logits.shape[:-1], dtype=torch.float32, device=dev)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_log_probs_from_logits_and_actions_f32(
         _ptr(policy_logits), _ptr(actions), rows, A, _ptr(out), _stream(dev))
   _lib.check(rc, 'vtr_log_probs_from_logits_and_actions_f32')
@@ -245,7 +264,7 @@ def pg_loss(logits: torch.Tensor, actions: torch.Tensor,
   rows = logits.numel() // A
   loss = torch.empty(1, dtype=torch.float32, device=dev)
   ws, nbytes = _loss_workspace(rows, dev)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_policy_gradient_loss_f32(
         _ptr(logits), _ptr(actions), _ptr(advantages), rows, A, _ptr(loss),
         _ptr(ws), nbytes, _stream(dev))
@@ -265,7 +284,7 @@ def pg_loss_bwd(logits: torch.Tensor, actions: torch.Tensor,
   dev = _check_cuda(logits, actions, advantages, grad_out)
   A = logits.shape[-1]
   d_logits = torch.empty_like(logits)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_policy_gradient_loss_bwd_f32(
         _ptr(logits), _ptr(actions), _ptr(advantages), _ptr(grad_out),
         logits.numel() // A, A, _ptr(d_logits), _stream(dev))
@@ -286,7 +305,7 @@ def entropy_loss(logits: torch.Tensor) -> torch.Tensor:
   rows = logits.numel() // A
   loss = torch.empty(1, dtype=torch.float32, device=dev)
   ws, nbytes = _loss_workspace(rows, dev)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_entropy_loss_f32(
         _ptr(logits), rows, A, _ptr(loss), _ptr(ws), nbytes, _stream(dev))
   _lib.check(rc, 'vtr_entropy_loss_f32')
@@ -304,7 +323,7 @@ def entropy_loss_bwd(logits: torch.Tensor, grad_out: torch.Tensor) -> torch.Tens
   dev = _check_cuda(logits, grad_out)
   A = logits.shape[-1]
   d_logits = torch.empty_like(logits)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_entropy_loss_bwd_f32(
         _ptr(logits), _ptr(grad_out), logits.numel() // A, A, _ptr(d_logits),
         _stream(dev))
@@ -324,7 +343,7 @@ def baseline_loss(advantages: torch.Tensor) -> torch.Tensor:
   n = advantages.numel()
   loss = torch.empty(1, dtype=torch.float32, device=dev)
   ws, nbytes = _loss_workspace(n, dev)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_baseline_loss_f32(
         _ptr(advantages), n, _ptr(loss), _ptr(ws), nbytes, _stream(dev))
   _lib.check(rc, 'vtr_baseline_loss_f32')
@@ -342,7 +361,7 @@ def baseline_loss_bwd(advantages: torch.Tensor,
   require_cuda()
   dev = _check_cuda(advantages, grad_out)
   d_adv = torch.empty_like(advantages)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_baseline_loss_bwd_f32(
         _ptr(advantages), _ptr(grad_out), advantages.numel(), _ptr(d_adv),
         _stream(dev))
@@ -360,7 +379,7 @@ def scale_inplace(x: torch.Tensor, scale: torch.Tensor) -> None:
   """x *= scale (device scalar), a no-op launch when scale == 1."""
   require_cuda()
   dev = _check_cuda(x, scale)
-  with torch.cuda.device(dev):
+  with _on(dev):
     rc = _lib.load().vtr_scale_inplace_f32(
         _ptr(x), _ptr(scale), x.numel(), _stream(dev))
   _lib.check(rc, 'vtr_scale_inplace_f32')
