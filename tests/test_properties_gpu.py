@@ -96,7 +96,8 @@ def test_softmax_shift_invariance(batch):
   out2, d_logits2, d_values2 = _run(batch, behaviour=batch['behaviour'] - 2 * shift,
                                     target=batch['target'] + shift)
   def close(a, b, tol, what):
-    err = float(((a.double() - b.double()).abs() / b.double().abs().clamp(min=1)).max())
+    a, b = a.detach().double(), b.detach().double()
+    err = float(((a - b).abs() / b.abs().clamp(min=1)).max())
     assert err <= tol, (what, err)
   close(out2.vtrace_returns.vs, out.vtrace_returns.vs, 2e-5, 'vs')
   close(out2.vtrace_returns.pg_advantages, out.vtrace_returns.pg_advantages, 2e-5, 'pg')
