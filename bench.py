@@ -40,6 +40,17 @@ def algorithmic_bytes(T, B, A):
   return T * B * (12 * A + 40) + 4 * B
 
 
+def workload_config(T, B, A, world, scaling):
+  """The `config` object; the same keys and values from both arms."""
+  return {
+      'workload': 'fused V-trace + IMPALA loss fwd+bwd, T=%d B=%d A=%d per GPU, '
+                  'all 5 V-trace fields + d_target_logits + d_values + 4 loss '
+                  'scalars' % (T, B, A),
+      'T': T, 'B_per_gpu': B, 'A': A, 'global_B': B * world,
+      'scaling': scaling, 'clip_rho': 1.0, 'clip_pg_rho': 1.0,
+      'baseline_cost': BASELINE_COST, 'entropy_cost': ENTROPY_COST}
+
+
 def measured_peak_gbs():
   path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
   try:
@@ -190,9 +201,9 @@ def run_reference(args):
       'ms_per_step': sec_per_step * 1e3, 'higher_is_better': True,
       'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
       'data': 'synthetic',
-      'config': {'workload': 'fused V-trace + IMPALA loss fwd+bwd, T=%d B=%d '
-                             'A=%d per GPU' % (T, args.B, A),
-                 'T': T, 'B_per_gpu': args.B, 'A': A, 'cpu_sample_B': B},
+      'config': workload_config(
+          T, args.B // args.gpus if args.scaling == 'strong' else args.B, A,
+          args.gpus, args.scaling),
       'cpu_baseline': {'value': rate, 'unit': UNIT, 'cores': cores,
                        'kind': 'port', 'sample': sample},
       'e2e': {'value': rate, 'unit': UNIT, 'h2d_bytes_per_step': 0,
@@ -235,13 +246,18 @@ class FusedCall(object):
     self.p = p
     self.inp = inp
     self.stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    self.describe()
+
+  def describe(self):
+    """What a call launches, for the parameters as they are now."""
     count = ctypes.c_int(0)
     text = ctypes.create_string_buffer(512)
-    rc = self.lib.vtr_fused_describe(ctypes.byref(p), 1, ctypes.byref(count), text, 512)
+    rc = self.lib.vtr_fused_describe(ctypes.byref(self.p), 1, ctypes.byref(count), text, 512)
     if rc != 0:
-      _lib.check(rc, 'vtr_fused_describe')
+      self._lib_mod.check(rc, 'vtr_fused_describe')
     self.launches_per_call = count.value     # kernels of this library per call
     self.plan = text.value.decode().strip()
+    return self.plan
 
   def __call__(self, stream=None):
     rc = self.lib.vtr_from_logits_fused_f32(
@@ -270,9 +286,10 @@ def run_gpu(args):
     if B % (4 * world):
       raise SystemExit('bench.py --scaling strong: B must be a multiple of 4 * ranks')
     B //= world
-  # at least 10 untimed steps: the per-SM speed table behind the tile sizes
-  # settles within a handful of calls
-  K, W = args.steps, max(args.warmup, 10)
+  K, W = args.steps, args.warmup
+  # The per-SM speed table behind the tile sizes settles within a handful of
+  # calls: a short, unreported pre-pass makes sure of that whatever --warmup is.
+  PRE = max(0, 10 - W)
 
   # Inputs + outputs of one step must not fit the 126 MB L2, or steps would be
   # served from it: small per-GPU batches (strong scaling) rotate over several
@@ -319,7 +336,9 @@ def run_gpu(args):
     call = calls[turn[0] % n_sets]
     turn[0] += 1
     if fused_exchange:
-      exchange.attach(call.p, global_losses)
+      # every step publishes its scalars and hands out the sums of the step
+      # before (already in this rank's buffer): no rank waits for another
+      exchange.attach(call.p, global_losses, lag=args.exchange_lag)
       call()
       return
     call()
@@ -331,7 +350,7 @@ def run_gpu(args):
       dist.barrier()
     torch.cuda.synchronize()
 
-  for _ in range(W):
+  for _ in range(PRE + W):
     step()
   barrier()
 
@@ -368,8 +387,95 @@ def run_gpu(args):
   kernel_mean_ms = total_ms / K      # max over ranks of the mean time per call
   value = T * B * world * K / (total_ms * 1e-3)
 
-  # ---- end to end through the public API with host buffers ---------------
+  # ---- are the cross-GPU sums right? ---------------------------------------
+  # Two more steps A, B with the exchange of the timed loop; the sums it hands
+  # out must equal, bit for bit, the rank-ordered float64 sum of the ranks'
+  # local losses gathered with NCCL.
+  exchange_check = None
+  if world > 1:
+    exchange_check = {'ok': None, 'ranks': world,
+                      'reason': 'no peer-memory exchange in this run (%s)' % exchange_kind}
+  if world > 1 and exchange is not None:
+    def rank_ordered_sum(local):
+      dist.all_gather_into_tensor(gathered, local)
+      total = gathered[0].double()
+      for r in range(1, world):          # rank 0, 1, ...: the order the kernel uses
+        total = total + gathered[r].double()
+      return total.float()
+
+    pairs = []
+    if fused_exchange:
+      call_a, call_b = calls[0], calls[1 % n_sets]
+      exchange.attach(call_a.p, global_losses, lag=args.exchange_lag)
+      call_a()
+      local_a = call_a.out['losses'].clone()
+      sums_a = global_losses.clone() if args.exchange_lag == 0 else None
+      exchange.attach(call_b.p, global_losses, lag=args.exchange_lag)
+      call_b()
+      local_b = call_b.out['losses'].clone()
+      if args.exchange_lag == 0:
+        pairs = [(sums_a, local_a), (global_losses.clone(), local_b)]
+      else:
+        pairs = [(global_losses.clone(), local_a), (exchange.collect(), local_b)]
+    else:
+      call_a = calls[0]
+      call_a()
+      pairs = [(exchange.all_sum(call_a.out['losses']).clone(), call_a.out['losses'].clone())]
+    worst, ok = 0.0, True
+    for got, local in pairs:
+      want = rank_ordered_sum(local)
+      finite = bool(torch.isfinite(got).all().item())
+      ok = ok and finite and torch.equal(got, want)
+      if finite:
+        worst = max(worst, float((got.double() - want.double()).abs().max().item()))
+    flag = torch.tensor([1 if ok else 0], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)       # every rank must agree
+    exchange_check = {'ok': bool(int(flag.item())), 'ranks': world,
+                      'max_abs_diff': worst, 'steps_checked': len(pairs),
+                      'against': 'nccl all_gather + rank-ordered float64 sum, bitwise'}
+    barrier()
+
+  # ---- the advertised Python API with device-resident inputs ---------------
+  # experiment.compute_vtrace_loss(...) + backward(): what a user of the
+  # drop-in gets per step when the learner's tensors already live on the GPU.
   from scalable_agent_b200 import experiment
+  api_in = {k: v for k, v in inp.items()}
+  api_in['target_policy_logits'] = inp['target_policy_logits'].detach().requires_grad_(True)
+  api_in['values'] = inp['values'].detach().requires_grad_(True)
+
+  def api_step():
+    api_in['target_policy_logits'].grad = None
+    api_in['values'].grad = None
+    out = experiment.compute_vtrace_loss(
+        baseline_cost=BASELINE_COST, entropy_cost=ENTROPY_COST, **api_in)
+    out.total_loss.backward()
+
+  for _ in range(max(3, W)):
+    api_step()
+  barrier()
+  a_begin = torch.cuda.Event(enable_timing=True)
+  a_end = torch.cuda.Event(enable_timing=True)
+  a_begin.record()
+  h0 = time.perf_counter()
+  for _ in range(K):
+    api_step()
+  host_s = time.perf_counter() - h0
+  a_end.record()
+  barrier()
+  api_ms = a_begin.elapsed_time(a_end) / K
+  if world > 1:
+    t = torch.tensor([api_ms], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    api_ms = float(t.item())
+  api_device = {
+      'value': T * B * world / (api_ms * 1e-3), 'unit': UNIT,
+      'ms_per_step': api_ms, 'host_ms_per_step': host_s / K * 1e3,
+      'vs_kernel': api_ms / (total_ms / K),
+      'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + backward, '
+             'device-resident inputs, CUDA events'}
+  del api_in
+
+  # ---- end to end through the public API with host buffers ---------------
   e2e_steps = max(1, min(K, 10))
   host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v)
           for k, v in inp.items()}
@@ -409,12 +515,16 @@ def run_gpu(args):
     peak, peak_src = measured_peak_gbs()
     alg = algorithmic_bytes(T, B, A)
     achieved = alg / (kernel_mean_ms * 1e-3) / 1e9
-    traffic = None
+    # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel is
+    # not measurable from inside this process: it is copied from the last
+    # `ncu --set full` capture of this shape (refreshed whenever K1c changes).
+    traffic, traffic_src = None, None
     try:
       with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as f:
         rec = json.load(f)
       if rec.get('T') == T and rec.get('B') == B and rec.get('A') == A:
         traffic = rec.get('dram_bytes_per_launch')
+        traffic_src = 'profiles/dram_traffic.json <- %s' % rec.get('source', 'ncu capture')
     except Exception:  # pylint: disable=broad-except
       pass
     line = {
@@ -422,14 +532,11 @@ def run_gpu(args):
         'steps': K, 'warmup': W, 'ms_per_step': total_ms / K,
         'higher_is_better': True, 'scaling': args.scaling, 'vs_baseline': None,
         'dtype': 'f32', 'data': 'synthetic',
-        'config': {
-            'workload': 'fused V-trace + IMPALA loss fwd+bwd, T=%d B=%d A=%d '
-                        'per GPU, all 5 V-trace fields + d_target_logits + '
-                        'd_values + 4 loss scalars written' % (T, B, A),
-            'T': T, 'B_per_gpu': B, 'A': A, 'global_B': B * world,
+        'config': workload_config(T, B, A, world, args.scaling),
+        'run': {
             'parallelism': ('single GPU' if world == 1 else
-                            'B sharded over %d ranks; sum of 4 loss scalars '
-                            'per step via %s' % (world, exchange_kind)),
+                            'B sharded over %d ranks (%d columns each); sum of 4 '
+                            'loss scalars per step via %s' % (world, B, exchange_kind)),
             'l2': ('no flush: %.0f MB of inputs + %.0f MB of outputs per step '
                    'exceed the 126 MB L2' % (
                        (T * B * (8 * A + 16) + 4 * B) / 1e6,
@@ -437,11 +544,11 @@ def run_gpu(args):
                    'no flush: steps rotate over %d independent sets of tensors, '
                    '%.0f MB in all, more than the 126 MB L2' % (
                        n_sets, n_sets * step_bytes / 1e6)),
-            'clip_rho': 1.0, 'clip_pg_rho': 1.0,
-            'baseline_cost': BASELINE_COST, 'entropy_cost': ENTROPY_COST},
+            'untimed_pre_pass_steps': PRE},
         'roofline': {
             'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
             'frac': achieved / peak, 'traffic': traffic,
+            'traffic_source': traffic_src,
             'peak_source': peak_src,
             'algorithmic_bytes_per_launch': alg,
             'kernel': call.plan + ' (time = timed region / steps: the whole '
@@ -454,6 +561,8 @@ def run_gpu(args):
                 'ms_per_step': e2e_s / e2e_steps * 1e3,
                 'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + '
                        'backward, pinned host inputs'},
+        'api_device': api_device,
+        'exchange_check': exchange_check,
         'gpu_launches': (call.launches_per_call +
                          (0 if exchange is None or fused_exchange else 2)) * K,
         'clocks': dict(sampler.summary(), sampled=clock_note),
@@ -474,6 +583,9 @@ def run_gpu(args):
     print(json.dumps(line), flush=True)
   if world > 1:
     dist.destroy_process_group()
+  if exchange_check is not None and exchange_check.get('ok') is False:
+    raise SystemExit('bench.py: the cross-GPU loss sums do not match the NCCL '
+                     'reference: %s' % json.dumps(exchange_check))
 
 
 def main():
@@ -490,6 +602,9 @@ def main():
   ap.add_argument('--no-cpu-baseline', action='store_true')
   ap.add_argument('--exchange', default='fused', choices=['fused', 'p2p', 'nccl'],
                   help='how the loss scalars are summed over ranks (N > 1)')
+  ap.add_argument('--exchange-lag', type=int, default=1, choices=[0, 1],
+                  help='fused exchange: 1 = each step hands out the sums of the '
+                       'step before (no rendezvous inside the step), 0 = its own')
   args = ap.parse_args()
   if args.impl == 'reference':
     run_reference(args)

@@ -103,6 +103,41 @@ def main():
     else:
       params = [torch.nn.Parameter(torch.randn(n, device=device))]
       opt = optim.RMSPropOptimizer(params, LR, DECAY, MOMENTUM, EPSILON, group=dist.group.WORLD)
+      # optim_check: a few steps of the fused kernel against the same steps
+      # from library parts (ncclAllReduce of the gradients in rank order is
+      # not guaranteed, so the reference is an all-gather + rank-ordered sum,
+      # then vtr_rmsprop_f32); parameters must be the same bits on every rank
+      # and equal to the reference.
+      ref_var = params[0].detach().clone()
+      ref_ms = torch.ones(n, device=device)
+      gathered = torch.empty(world * n, device=device) if n <= 16000000 else None
+      check = {'ok': None, 'reason': 'skipped above 16 M parameters'}
+      if gathered is not None:
+        gen = torch.Generator(device=device).manual_seed(1234 + rank)
+        ok = True
+        for _ in range(3):
+          params[0].grad.copy_(torch.randn(n, generator=gen, device=device))
+          dist.all_gather_into_tensor(gathered, params[0].grad)
+          total = gathered[:n].clone()
+          for r in range(1, world):
+            total += gathered[r * n:(r + 1) * n]
+          opt.step()
+          rc = lib.vtr_rmsprop_f32(ref_var.data_ptr(), ref_ms.data_ptr(), None, total.data_ptr(),
+                                   n, LR, DECAY, 0.0, EPSILON, stream)
+          assert rc == 0, _lib.last_error()
+        torch.cuda.synchronize()
+        opt.check_peers()
+        same_as_ref = torch.equal(params[0].detach(), ref_var)
+        mine = params[0].detach().clone()
+        dist.broadcast(mine, src=0)
+        same_on_all = torch.equal(mine, params[0].detach())
+        flag = torch.tensor([1 if (same_as_ref and same_on_all) else 0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        check = {'ok': bool(int(flag.item())), 'steps': 3,
+                 'max_abs_diff': float((params[0].detach() - ref_var).abs().max().item()),
+                 'against': 'all_gather + rank-ordered sum + vtr_rmsprop_f32, bitwise; '
+                            'identical parameters on all ranks'}
+        del gathered
       params[0].grad.normal_()
       us = max_over_ranks(timed(opt.step, args.steps, args.warmup, barrier))
       opt.check_peers()
@@ -111,6 +146,7 @@ def main():
       # slices); out of it: the mirror image
       per_direction = 2 * (opt.hi - opt.lo) * 4 * (world - 1)
       lines.append({'impl': 'fused', 'n_gpus': world, 'params': n, 'us_per_step': us,
+                    'optim_check': check,
                     'nvlink_bytes_per_direction_per_rank': per_direction,
                     'nvlink_gbs_per_direction': per_direction / us * 1e-3})
       del opt, params
@@ -134,6 +170,9 @@ def main():
   if world > 1:
     dist.barrier()
     dist.destroy_process_group()
+  if any(l.get('optim_check', {}).get('ok') is False for l in lines):
+    raise SystemExit('optim_bench.py: the fused all-reduce + RMSProp step does not match '
+                     'the reference')
 
 
 if __name__ == '__main__':

@@ -10,6 +10,7 @@ L2, as they would right after the network's heads produced them).  One JSON
 line per (shape, path).  This is a diagnostic; `bench.py` is the contract.
 """
 import argparse
+import ctypes
 import json
 import os
 import statistics
@@ -64,6 +65,7 @@ def main():
         call = bench.FusedCall(inp, T, B, A, device)
         call.p.path = _lib.PATHS[path]
         try:
+          call.describe()
           for _ in range(5):
             call()
           torch.cuda.synchronize()
@@ -95,11 +97,38 @@ def main():
         sampler.stop()
         clocks = sampler.summary()
         warm_us = s.elapsed_time(e) * 1e3 / iters
+        # The same calls replayed from a CUDA graph: no Python, ctypes or
+        # launch API between the kernels, so this is what the GPU itself needs
+        # per call (for the small shapes `warm` is the host's launch rate).
+        graph_us = None
+        try:
+          per_graph = 20
+          side = torch.cuda.Stream()
+          side.wait_stream(torch.cuda.current_stream())
+          graph = torch.cuda.CUDAGraph()
+          with torch.cuda.graph(graph, stream=side):
+            cap = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            for _ in range(per_graph):
+              call(cap)
+          for _ in range(3):
+            graph.replay()
+          torch.cuda.synchronize()
+          reps = max(2, iters // per_graph)
+          s.record()
+          for _ in range(reps):
+            graph.replay()
+          e.record()
+          torch.cuda.synchronize()
+          graph_us = s.elapsed_time(e) * 1e3 / (reps * per_graph)
+          del graph
+        except Exception as err:  # pylint: disable=broad-except
+          print('%s path=%s: no graph timing: %s' % (name, path, str(err).splitlines()[0][:120]))
         alg = bench.algorithmic_bytes(T, B, A)
         cold_us = statistics.median(cold)
         rec = {
             'shape': name, 'T': T, 'B': B, 'A': A, 'path': path,
-            'cold_us': cold_us, 'warm_us': warm_us,
+            'cold_us': cold_us, 'warm_us': warm_us, 'graph_us': graph_us,
+            'plan': call.plan,
             'timesteps_per_s_warm': T * B / (warm_us * 1e-6),
             'GBps_cold': alg / cold_us / 1e3, 'GBps_warm': alg / warm_us / 1e3,
             'frac_peak_warm': alg / warm_us / 1e3 / peak,
@@ -107,8 +136,9 @@ def main():
         }
         f.write(json.dumps(rec) + '\n')
         f.flush()
-        print('%-24s path=%-6s cold %8.1f us  warm %8.1f us  %7.0f GB/s (%.2f of peak) '
-              'roofline %.1f us  sm %s MHz %s' % (name, path, cold_us, warm_us, rec['GBps_warm'],
+        print('%-24s path=%-6s cold %8.1f us  warm %8.1f us  graph %s us  %7.0f GB/s (%.2f of peak) '
+              'roofline %.1f us  sm %s MHz %s' % (name, path, cold_us, warm_us,
+                                    '%8.1f' % graph_us if graph_us else '     n/a', rec['GBps_warm'],
                                     rec['frac_peak_warm'], rec['roofline_us'],
                                     clocks['sm_mhz'], ','.join(clocks['reasons'])))
       del inp

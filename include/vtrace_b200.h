@@ -61,6 +61,7 @@ extern "C" {
 #define VTR_PATH_COLUMN 1  /* 32-column tiles, one ring per tile (any alignment) */
 #define VTR_PATH_SM_TILE 2 /* one wide tile per SM, shared ring (16-B aligned)  */
 #define VTR_PATH_ITEM 3    /* one thread per (t, b) item: small B, T <= 256      */
+#define VTR_PATH_CHUNK 4   /* T split over a thread-block cluster: mid-sized B   */
 
 int vtr_version(void);
 
@@ -139,10 +140,17 @@ typedef struct vtr_fused_params {
   int32_t exchange_rank;
   int32_t exchange_world;
   uint32_t exchange_seq;
-  uint32_t reserved2;
+  /* Which step's sums `exchange_sums` receives: 0 = this call's (the launch
+     then ends only when the slowest rank has published: every step pays the
+     rendezvous), 1 = the previous call's, seq - 1 (they are normally in this
+     rank's buffer already, so no rank waits for another and the ranks may
+     drift by a step; nothing is written when seq == 1).  The last step's sums
+     are then fetched with vtr_exchange_collect_f32. */
+  uint32_t exchange_lag;
   /* float[4] or NULL: if given, the pass also does vtr_exchange_collect_f32's
-     part (wait for every rank's scalars of this seq, at most 2 s, and write
-     their rank-ordered sum here), so a step needs no exchange call at all. */
+     part (wait for every rank's scalars of step seq - exchange_lag, at most
+     2 s, and write their rank-ordered sum here), so a step needs no exchange
+     call at all. */
   float* exchange_sums;
 } vtr_fused_params;
 
@@ -178,9 +186,14 @@ int vtr_fused_describe(const vtr_fused_params* p, int have_workspace, int* num_k
    cudaMalloc would fail or stall the other streams by synchronising the
    device.  The tile partials go to a 200 KiB array built into the library
    (every GPU that loads the library holds it until the process exits); the
-   caller still passes all inputs and outputs in `p`.  Results are identical to
-   vtr_from_logits_fused_f32.
-   - p->B must be <= VTR_NOALLOC_MAX_B, else VTR_ERR_UNSUPPORTED.
+   caller still passes all inputs and outputs in `p`.  Per-column outputs are
+   what vtr_from_logits_fused_f32 gives; the losses may differ from its in the
+   last bit, because once a batch is too wide for the preferred kernel's
+   partials to fit the array another kernel, with another summation order,
+   takes over (8192 < B/4, i.e. B > 32768 on the per-SM kernel).
+   - p->B must be <= VTR_NOALLOC_MAX_B, else VTR_ERR_UNSUPPORTED; so is an
+     explicit p->path whose kernel's partials do not fit the array.
+   - With p->losses and p->losses_f64 both NULL the array is not used.
    - No cudaMalloc/cudaFree or allocating library routine is called.
    - The first call on each device looks the array's address up (with that
      device current); make that first call before any stream capture.
@@ -263,13 +276,17 @@ int vtr_baseline_loss_bwd_f32(const float* advantages, const float* grad_out,
  * device pointers to those buffers as mapped on this rank, its own included.
  * Per step, with `seq` = 1, 2, 3, ... identical on all ranks:
  *   vtr_exchange_publish_f32: stores values[0..n) and then seq into slot
- *     [seq & 1][rank] of every peer's buffer (n <= 6);
+ *     [seq % 4][rank] of every peer's buffer (n <= 6);
  *   vtr_exchange_collect_f32: waits (at most 2 s, then writes NaN) until all
- *     `world` slots of parity seq & 1 in this rank's buffer carry seq, and
- *     writes their sum, accumulated in double in rank order, to sums[0..n).
+ *     `world` slots of step seq in this rank's buffer carry seq, and writes
+ *     their sum, accumulated in double in rank order, to sums[0..n).
+ * A slot is reused four steps later: a rank must have collected step seq - 2
+ * (itself or through exchange_sums) before it publishes step seq; it may
+ * publish one step without collecting the one before (exchange_lag = 1).
  */
 #define VTR_EXCHANGE_MAX_RANKS 16
 #define VTR_EXCHANGE_SLOT_FLOATS 8
+#define VTR_EXCHANGE_SLOTS 4
 size_t vtr_exchange_buffer_bytes(int32_t world);
 int vtr_exchange_publish_f32(const float* values, int32_t n, void* const* peer_buffers, int32_t rank,
                              int32_t world, uint32_t seq, void* stream);
@@ -308,15 +325,30 @@ int vtr_rmsprop_f32(float* var, float* ms, float* mom, const float* grad, int64_
  * 2, 3, ... and hyper-parameters; when the call has completed on a rank, that
  * rank's parameter buffer holds the updated values of all slices and its
  * gradient buffer may be overwritten.  Gradients are summed in rank order, so
- * all ranks hold the same bits.  A peer that does not show up within 2 s sets
- * word 33 of this rank's sync buffer to 1 instead of hanging the GPU.
+ * all ranks hold the same bits.
+ *
+ * A peer that does not show up must not hang the GPU: a rank waits at most the
+ * peer time-out (vtr_set_peer_timeout_ms, 20 s unless changed) and then gives
+ * the step up.  The decision is taken once per launch, so a rank's slice is
+ * updated completely or not at all; the rank that gives up sets word 33 of its
+ * sync buffer (sticky) and, if `host_status` is given, stores seq there - a
+ * uint32 in pinned host memory that the caller can look at without
+ * synchronising the device - and marks its flags in every peer's sync buffer,
+ * so that a peer waiting for it, or arriving later, gives the step up too and
+ * flags it the same way.  After a flagged step the ranks' parameters may
+ * differ; the caller has to re-synchronise them (e.g. broadcast).
  */
 int vtr_rmsprop_slice(int64_t n, int32_t world, int32_t rank, int64_t* lo, int64_t* hi);
 size_t vtr_rmsprop_sync_bytes(void);
 int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* grad_peers, void* const* sync_peers,
                               float* ms_slice, float* mom_slice, int64_t n, int32_t rank, int32_t world,
                               uint32_t seq, float learning_rate, float decay, float momentum,
-                              float epsilon, void* stream);
+                              float epsilon, uint32_t* host_status, void* stream);
+/* How long vtr_rmsprop_allreduce_f32 waits for a peer (process-wide; read at
+   launch).  Learner ranks drift apart by much more than a kernel's length now
+   and then - a late actor batch, a checkpoint - so keep it well above that. */
+void vtr_set_peer_timeout_ms(uint64_t milliseconds);
+uint64_t vtr_get_peer_timeout_ms(void);
 
 /* x[i] *= *scale for i < n, skipped entirely when *scale == 1.  `scale` is a
    device float[1].  Used to apply the upstream gradient of the total loss

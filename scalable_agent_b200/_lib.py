@@ -17,7 +17,7 @@ VTR_MAX_ACTIONS = 256
 FLAG_NO_CLIP_RHO = 1
 FLAG_NO_CLIP_PG_RHO = 2
 REWARD_CLIP_MODES = {None: 0, 'none': 0, 'abs_one': 1, 'soft_asymmetric': 2}
-PATHS = {None: 0, 'auto': 0, 'column': 1, 'sm_tile': 2, 'item': 3}
+PATHS = {None: 0, 'auto': 0, 'column': 1, 'sm_tile': 2, 'item': 3, 'chunk': 4}
 
 
 class FusedParams(ctypes.Structure):
@@ -54,7 +54,7 @@ class FusedParams(ctypes.Structure):
       ('exchange_rank', ctypes.c_int32),
       ('exchange_world', ctypes.c_int32),
       ('exchange_seq', ctypes.c_uint32),
-      ('reserved2', ctypes.c_uint32),
+      ('exchange_lag', ctypes.c_uint32),
       ('exchange_sums', ctypes.c_void_p),
   ]
 
@@ -107,7 +107,9 @@ SIGNATURES = {
     'vtr_rmsprop_allreduce_f32':
         (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
                         ctypes.POINTER(ctypes.c_void_p), _P, _P, _I64, _I32, _I32, _U32,
-                        _F, _F, _F, _F, _P]),
+                        _F, _F, _F, _F, _P, _P]),
+    'vtr_set_peer_timeout_ms': (None, [ctypes.c_uint64]),
+    'vtr_get_peer_timeout_ms': (ctypes.c_uint64, []),
 }
 
 _lib = None

@@ -9,17 +9,23 @@
 namespace vtr {
 
 constexpr int kSlotFloats = VTR_EXCHANGE_SLOT_FLOATS;
+// Buffer of one rank: float[kExchangeSlots][world][8]; slot [seq % 4][r] holds
+// rank r's values of step seq in [0..5] and seq itself in [7].  Four slots let
+// a rank run ahead: it publishes step s+4 (which reuses the slot of step s)
+// only after it has collected step s+2, which needs every peer's publish of
+// s+2, which that peer's stream orders after its own collect of step s.
+constexpr uint32_t kExchangeSlots = VTR_EXCHANGE_SLOTS;
 
 struct PeerBuffers {
   float* p[VTR_EXCHANGE_MAX_RANKS];
 };
 
-// Stores values[0..n) and then the sequence number into slot [seq & 1][rank]
+// Stores values[0..n) and then the sequence number into slot [seq % 4][rank]
 // of ONE peer's buffer: values first, a system-wide fence, then the flag with
 // release semantics, so a peer that sees the flag sees the values.
 __device__ __forceinline__ void exchange_publish_to_peer(float* peer, const float* values, int n,
                                                          int rank, int world, uint32_t seq) {
-  float* slot = peer + (static_cast<size_t>(seq & 1u) * world + rank) * kSlotFloats;
+  float* slot = peer + (static_cast<size_t>(seq % kExchangeSlots) * world + rank) * kSlotFloats;
   for (int i = 0; i < n; ++i) slot[i] = values[i];
   __threadfence_system();
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(slot + 7)),
@@ -30,7 +36,7 @@ __device__ __forceinline__ void exchange_publish_to_peer(float* peer, const floa
 // The same for exactly four values held in registers.
 __device__ __forceinline__ void exchange_publish4_to_peer(float* peer, float v0, float v1, float v2,
                                                           float v3, int rank, int world, uint32_t seq) {
-  float* slot = peer + (static_cast<size_t>(seq & 1u) * world + rank) * kSlotFloats;
+  float* slot = peer + (static_cast<size_t>(seq % kExchangeSlots) * world + rank) * kSlotFloats;
   *reinterpret_cast<float4*>(slot) = make_float4(v0, v1, v2, v3);  // slots are 32-byte aligned
   __threadfence_system();
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(slot + 7)),
@@ -40,14 +46,14 @@ __device__ __forceinline__ void exchange_publish4_to_peer(float* peer, float v0,
 
 constexpr unsigned long long kExchangeTimeoutNs = 2000000000ull;  // 2 s
 
-// Called by one whole warp.  Lane r waits until rank r's slot of parity
-// seq & 1 in this rank's own buffer carries `seq`, then lane 0 sums the slots
+// Called by one whole warp.  Lane r waits until rank r's slot of step `seq`
+// in this rank's own buffer carries `seq`, then lane 0 sums the slots
 // in rank order in double.  A peer that never publishes must not hang the GPU:
 // after the timeout the sums are NaN.
 __device__ __forceinline__ void exchange_collect_warp(const float* mine, int n, int world, uint32_t seq,
                                                       float* sums, unsigned long long timeout_ns) {
   const int r = threadIdx.x & 31;
-  const float* base = mine + static_cast<size_t>(seq & 1u) * world * kSlotFloats;
+  const float* base = mine + static_cast<size_t>(seq % kExchangeSlots) * world * kSlotFloats;
   int ok = 1;
   if (r < world) {
     const uint32_t* flag = reinterpret_cast<const uint32_t*>(base + r * kSlotFloats + 7);

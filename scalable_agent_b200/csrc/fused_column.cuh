@@ -1,6 +1,7 @@
 // K1a of the fused pass (see vtrace_fused.cu).
 #pragma once
 #include "fused_common.cuh"
+#include "fused_finish.cuh"
 
 namespace vtr {
 
@@ -10,7 +11,8 @@ namespace vtr {
 // ring (5 slots at A=18) then runs ahead of the single consumer.
 // ---------------------------------------------------------------------------
 template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant__ FusedArgs a) {
+__global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant__ TileArgs args) {
+  const FusedArgs& a = args.f;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int A = A_CT > 0 ? A_CT : a.A;
   const int T = a.T, B = a.B;
@@ -181,8 +183,10 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
       double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
       out[0] = pg_sum, out[1] = bl_sum, out[2] = ent_sum;
     }
+    if (args.fin.ticket) finish_losses(a, args.fin);
   }
-  if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
+  // the bulk stores must have read their staging rows before the CTA goes away
+  if (GRADS && tma_out && lane == 0) ptx::bulk_wait_read<0>();
 }
 
 

@@ -1,6 +1,7 @@
 // K1b of the fused pass (see vtrace_fused.cu).
 #pragma once
 #include "fused_common.cuh"
+#include "fused_finish.cuh"
 
 namespace vtr {
 
@@ -26,7 +27,8 @@ namespace vtr {
 // at 80 registers, so that 24 warps fit an SM's register file.
 // ---------------------------------------------------------------------------
 template <int A_CT, bool GRADS>
-__global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ FusedArgs a) {
+__global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ TileArgs args) {
+  const FusedArgs& a = args.f;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int A = A_CT > 0 ? A_CT : a.A;
   const int T = a.T, B = a.B;
@@ -212,15 +214,19 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
     if (lane == 0)
       warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
     __syncthreads();
-    if (threadIdx.x == 0) {
-      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-      for (int w = 0; w < W; ++w)
-        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
-      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
-      out[0] = p0, out[1] = p1, out[2] = p2;
+    if (warp == 0) {
+      if (lane == 0) {
+        double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+        for (int w = 0; w < W; ++w)
+          p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
+        double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
+        out[0] = p0, out[1] = p1, out[2] = p2;
+      }
+      if (args.fin.ticket) finish_losses(a, args.fin);
     }
   }
-  if (GRADS && tma_out && lane == 0) ptx::bulk_wait<0>();
+  // the bulk stores must have read their staging rows before the CTA goes away
+  if (GRADS && tma_out && lane == 0) ptx::bulk_wait_read<0>();
 }
 
 

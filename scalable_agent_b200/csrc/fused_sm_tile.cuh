@@ -64,7 +64,8 @@ struct SmTileArgs {
   PeerBuffers ex_peers;
   int ex_rank, ex_world;
   uint32_t ex_seq;
-  float* ex_sums;  // or null: sum over ranks, collected by the same tile
+  uint32_t ex_lag;  // ex_sums receives the sums of step ex_seq - ex_lag
+  float* ex_sums;   // or null: sum over ranks, collected by the same tile
 };
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
@@ -462,10 +463,10 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
                                         static_cast<float>(ent), static_cast<float>(total), args.ex_rank,
                                         args.ex_world, args.ex_seq);
             }
-            if (args.ex_world > 0 && args.ex_sums) {
+            if (args.ex_world > 0 && args.ex_sums && args.ex_seq > args.ex_lag) {
               __syncwarp();
-              exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world, args.ex_seq,
-                                    args.ex_sums, kExchangeTimeoutNs);
+              exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world,
+                                    args.ex_seq - args.ex_lag, args.ex_sums, kExchangeTimeoutNs);
             }
             if (lane == 0) {
               if (a.losses) {

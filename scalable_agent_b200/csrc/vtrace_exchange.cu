@@ -8,10 +8,7 @@
 // sequence number, and sums what has arrived in rank order.  The sum is
 // bitwise identical on all ranks.
 //
-// Buffer of one rank: float[2][world][8]; slot [seq & 1][r] holds rank r's
-// values in [0..5] and the sequence number in [7].  Two parities suffice: rank
-// Y can publish step s+2 only after collecting step s+1, which needs X's
-// publish of s+1, which X's stream orders after its collect of step s.
+// Buffer layout and the slot-reuse argument: exchange.cuh.
 #include "common.h"
 #include "exchange.cuh"
 
@@ -40,7 +37,7 @@ using vtr::fail;
 
 extern "C" size_t vtr_exchange_buffer_bytes(int32_t world) {
   if (world <= 0 || world > VTR_EXCHANGE_MAX_RANKS) return 0;
-  return sizeof(float) * 2 * world * VTR_EXCHANGE_SLOT_FLOATS;
+  return sizeof(float) * VTR_EXCHANGE_SLOTS * world * VTR_EXCHANGE_SLOT_FLOATS;
 }
 
 namespace vtr {

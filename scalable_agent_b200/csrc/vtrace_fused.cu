@@ -16,17 +16,26 @@
 //   K1b fused_relay_kernel    fused_relay.cuh    32-column tile, W warps relaying the carry
 //   K1c fused_sm_tile_kernel  fused_sm_tile.cuh  one wide tile per SM, producer/consumer ring,
 //                                                speed-weighted tiles, in-kernel final reduction
-//   K2  fused_item_kernel     fused_item.cuh     one thread per (t, b) item, tiny batches
-//   K3  reduce_losses_kernel  (below)            second stage of the loss reduction
+//   K2  fused_item_kernel     fused_item.cuh     one thread per (t, b) item, tiny batches;
+//                                                warp-shuffle affine scan over T
+//   K5  fused_chunk_kernel    fused_chunk.cuh    T split over a thread-block cluster, chunk
+//                                                aggregates through distributed shared memory
+//   K3  reduce_losses_kernel  (below)            second stage of the loss reduction, when it
+//                                                is not done by the last CTA of K2/K5
 // Losses accumulate per lane in double and are reduced in fixed orders; the
-// only atomics are two tickets in K1c (which tile next, who finished last).
+// only atomics are tickets (which tile next in K1c, who finished last).
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "common.h"
+#include "fused_chunk.cuh"
 #include "fused_column.cuh"
 #include "fused_common.cuh"
+#include "fused_finish.cuh"
 #include "fused_item.cuh"
 #include "fused_relay.cuh"
 #include "fused_sm_tile.cuh"
@@ -92,11 +101,13 @@ static void record_plan(const char* fmt, ...) {
 }
 
 template <int A_CT, bool GRADS>
-static int launch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
+static int launch_tiles(const TileArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
   if (g_plan.dry_run) {
-    record_plan("%s<A=%d,%s> grid=%d warps/tile=%d ring=%d smem=%zu; ",
+    record_plan("%s<A=%d,%s> grid=%d warps/tile=%d ring=%d smem=%zu%s%s; ",
                 warps > 1 ? "fused_relay_kernel" : "fused_column_kernel", A_CT, GRADS ? "grads" : "fwd",
-                tiles, warps, args.depth, smem);
+                tiles, warps, args.f.depth, smem, args.fin.ticket ? " + in-kernel final reduction" : "",
+                args.fin.ex_world > 0 ? (args.fin.ex_sums ? " + peer publish + collect" : " + peer publish")
+                                      : "");
     return VTR_OK;
   }
   auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
@@ -107,8 +118,8 @@ static int launch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem
 }
 
 template <bool GRADS>
-static int dispatch_tiles(const FusedArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
-  switch (args.A) {
+static int dispatch_tiles(const TileArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
+  switch (args.f.A) {
     case 3: return launch_tiles<3, GRADS>(args, tiles, warps, smem, stream);
     case 4: return launch_tiles<4, GRADS>(args, tiles, warps, smem, stream);
     case 6: return launch_tiles<6, GRADS>(args, tiles, warps, smem, stream);
@@ -265,15 +276,16 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   if (const int pct = env_int("VTR_SM_SMOOTHING")) args.smoothing = 0.01f * pct;  // experiments only
   args.share_pct = 100;
   if (const int pct = env_int("VTR_SM_SHARE_PCT")) args.share_pct = min(100, max(1, pct));  // tests only
+
   if (balance) args.f.losses = p->losses, args.f.losses_f64 = p->losses_f64;
   *losses_done = balance;
   // The tile that finishes the reduction also publishes to the peers.
-  args.ex_world = 0, args.ex_rank = 0, args.ex_seq = 0, args.ex_sums = nullptr;
+  args.ex_world = 0, args.ex_rank = 0, args.ex_seq = 0, args.ex_lag = 0, args.ex_sums = nullptr;
   for (float*& q : args.ex_peers.p) q = nullptr;
   if (balance && p->exchange_peer_buffers) {
     if (int rc = fill_peer_buffers(&args.ex_peers, p->exchange_peer_buffers, p->exchange_world)) return rc;
     args.ex_world = p->exchange_world, args.ex_rank = p->exchange_rank, args.ex_seq = p->exchange_seq;
-    args.ex_sums = p->exchange_sums;
+    args.ex_lag = p->exchange_lag, args.ex_sums = p->exchange_sums;
     *exchange_done = true;
   }
 
@@ -322,62 +334,302 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
                : dispatch_sm_tile<false>(args, grid, smem, stream);
 }
 
-// VTR_PATH_AUTO takes K2 for the smallest batches only: its threads read their
-// rows straight from global memory, 72-byte pieces 2 MB apart, which is fine
-// for a few hundred columns and slower than K1b's ring beyond (measured at
-// T=100 A=18: B=256 14 us vs 25 us, B=512 20 us vs 25 us, B=1024 29 us vs 26 us,
-// B=2048 50 us vs 23 us).
-constexpr int kItemAutoColumns = 512;
-static bool item_kernel_applies(const vtr_fused_params* p) {
-  return p->T <= kItemMaxSteps && specialised_actions(p->A) && p->B <= kItemAutoColumns;
+// ---------------------------------------------------------------------------
+// Tickets for the in-kernel final reduction (fused_finish.cuh).  The "who
+// finished last" counter must be zero when a launch starts.  Zeroing it in the
+// caller's workspace would cost a second stream operation per call - as much
+// as the kernel itself on the small shapes - so the counters live in a ring
+// inside the library: zero at load, each launch takes the next one, and the
+// CTA that finishes last puts it back to zero.  A counter is handed out again
+// kTicketRing launches later; a GPU runs at most 128 kernels at a time, so two
+// launches never hold the same counter.  A launch that is being captured into
+// a graph will be replayed with the counter it was captured with, any number
+// of times and at any later moment, so it gets one of kTicketCaptured counters
+// that are never handed out again; once those are used up captured launches
+// leave the stage to K3.
+// ---------------------------------------------------------------------------
+constexpr int kTicketRing = 1024;
+constexpr int kTicketCaptured = 1024;
+static __device__ unsigned int g_finish_tickets[kTicketRing + kTicketCaptured];
+
+static int next_ticket(cudaStream_t stream, unsigned int** out) {
+  constexpr int kMaxDevices = 64;
+  static unsigned int* base[kMaxDevices] = {};
+  static std::mutex mu;
+  static std::atomic<unsigned int> turn{0}, captured{0};
+  *out = nullptr;
+  cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+  VTR_CUDA_CHECK(cudaStreamIsCapturing(stream, &capturing));
+  int dev = 0;
+  VTR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(VTR_ERR_UNSUPPORTED, "device index %d", dev);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!base[dev]) {
+      if (capturing != cudaStreamCaptureStatusNone) return VTR_OK;  // no symbol lookup while capturing
+      void* ptr = nullptr;
+      VTR_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_finish_tickets));
+      base[dev] = static_cast<unsigned int*>(ptr);
+    }
+  }
+  if (capturing != cudaStreamCaptureStatusNone) {
+    const unsigned int k = captured.fetch_add(1u, std::memory_order_relaxed);
+    if (k < static_cast<unsigned int>(kTicketCaptured)) *out = base[dev] + kTicketRing + k;
+    return VTR_OK;
+  }
+  *out = base[dev] + turn.fetch_add(1u, std::memory_order_relaxed) % kTicketRing;
+  return VTR_OK;
+}
+
+// Fills the in-kernel final stage of K2/K5.  `wanted`: losses were asked for
+// and the last CTA can afford the sum.  Sets *losses_done / *exchange_done to
+// what the launch will do itself.
+static int fill_finish(FinishArgs* fin, const vtr_fused_params* p, bool wanted, int num_ctas,
+                       int num_partials, cudaStream_t stream, bool* losses_done, bool* exchange_done) {
+  fin->ticket = nullptr;
+  fin->num_ctas = num_ctas, fin->num_partials = num_partials;
+  fin->losses = p->losses, fin->losses_f64 = p->losses_f64;
+  fin->ex_world = 0, fin->ex_rank = 0, fin->ex_seq = 0, fin->ex_lag = 0, fin->ex_sums = nullptr;
+  for (float*& q : fin->ex_peers.p) q = nullptr;
+  *losses_done = *exchange_done = false;
+  if (!wanted || getenv("VTR_NO_INKERNEL_FINISH")) return VTR_OK;
+  if (g_plan.dry_run) {
+    static unsigned int dummy;
+    fin->ticket = &dummy;  // never dereferenced
+  } else if (int rc = next_ticket(stream, &fin->ticket)) {
+    return rc;
+  }
+  if (!fin->ticket) return VTR_OK;
+  *losses_done = true;
+  if (p->exchange_peer_buffers) {
+    if (int rc = fill_peer_buffers(&fin->ex_peers, p->exchange_peer_buffers, p->exchange_world)) return rc;
+    fin->ex_world = p->exchange_world, fin->ex_rank = p->exchange_rank, fin->ex_seq = p->exchange_seq;
+    fin->ex_lag = p->exchange_lag, fin->ex_sums = p->exchange_sums;
+    *exchange_done = true;
+  }
+  return VTR_OK;
+}
+
+// K5.  Steps per chunk S (= warps per CTA) and chunks C (= CTAs per cluster):
+// about 12 steps per chunk, at most 8 chunks (the portable cluster size); a
+// longer unroll takes up to kChunkMaxChunks chunks if the device schedules
+// such clusters, and falls back to the 32-column-tile kernels otherwise.
+constexpr int kChunkMaxColumns = 16384;  // C partials per group stay within one per column
+
+static size_t chunk_smem_bytes(int A, int S) {
+  return kChunkBarrierBytes + static_cast<size_t>(S) * 64 * A * sizeof(float) +
+         (static_cast<size_t>(S) * 64 + kChunkMaxChunks * 64) * sizeof(float) +
+         static_cast<size_t>(S) * 3 * sizeof(double);
+}
+
+static bool chunk_shape(const vtr_fused_params* p, int* steps, int* chunks) {
+  if (p->B > kChunkMaxColumns) return false;
+  DeviceInfo dev;
+  if (device_info(&dev) != VTR_OK) return false;
+  int S = env_int("VTR_CHUNK_STEPS");
+  if (S <= 0) {
+    const int c0 = min(8, max(1, (p->T + 11) / 12));
+    S = (p->T + c0 - 1) / c0;
+  }
+  S = max(1, min(S, min(p->T, kChunkMaxSteps)));
+  while (S > 1 && chunk_smem_bytes(p->A, S) > static_cast<size_t>(dev.max_smem_optin)) --S;
+  if (chunk_smem_bytes(p->A, S) > static_cast<size_t>(dev.max_smem_optin)) return false;
+  const int C = (p->T + S - 1) / S;
+  if (C > kChunkMaxChunks) return false;
+  *steps = S, *chunks = C;
+  return true;
 }
 
 template <int A_CT, bool GRADS>
-static int launch_item(const FusedArgs& args, cudaStream_t stream) {
-  const int threads = ((args.T + 31) / 32) * 32;
+static int launch_chunk(const ChunkArgs& args, int groups, size_t smem, cudaStream_t stream) {
   if (g_plan.dry_run) {
-    record_plan("fused_item_kernel<A=%d,%s> grid=%d threads=%d; ", A_CT, GRADS ? "grads" : "fwd", args.B,
-                threads);
+    record_plan("fused_chunk_kernel<A=%d,%s> grid=%dx%d cluster=%d warps/cta=%d smem=%zu%s%s; ", A_CT,
+                GRADS ? "grads" : "fwd", args.chunks, groups, args.chunks, args.steps, smem,
+                args.fin.ticket ? " + in-kernel final reduction" : "",
+                args.fin.ex_world > 0 ? (args.fin.ex_sums ? " + peer publish + collect" : " + peer publish")
+                                      : "");
     return VTR_OK;
   }
-  fused_item_kernel<A_CT, GRADS><<<args.B, threads, 0, stream>>>(args);
+  auto kernel = fused_chunk_kernel<A_CT, GRADS>;
+  if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
+  if (args.chunks > 8) {
+    // Clusters of more than 8 CTAs are opt-in and may not be schedulable.
+    static std::mutex mu;
+    static int allowed[64] = {};  // per device: 0 unknown, 1 yes, -1 no (per template instance)
+    int dev = 0;
+    VTR_CUDA_CHECK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && allowed[dev] == 0)
+      allowed[dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) ==
+                             cudaSuccess
+                         ? 1
+                         : -1;
+    cudaGetLastError();
+    if (dev < 0 || dev >= 64 || allowed[dev] < 0)
+      return fail(VTR_ERR_UNSUPPORTED, "chunk kernel: clusters of %d CTAs are not available", args.chunks);
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(args.chunks, groups, 1);
+  cfg.blockDim = dim3(32 * args.steps, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = args.chunks;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (args.chunks > 8) {
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) != cudaSuccess || clusters < 1) {
+      cudaGetLastError();
+      return fail(VTR_ERR_UNSUPPORTED, "chunk kernel: a cluster of %d CTAs does not fit this device",
+                  args.chunks);
+    }
+  }
+  VTR_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, args));
+  return VTR_OK;
+}
+
+template <bool GRADS>
+static int dispatch_chunk(const ChunkArgs& args, int groups, size_t smem, cudaStream_t stream) {
+  switch (args.f.A) {
+    case 3: return launch_chunk<3, GRADS>(args, groups, smem, stream);
+    case 4: return launch_chunk<4, GRADS>(args, groups, smem, stream);
+    case 6: return launch_chunk<6, GRADS>(args, groups, smem, stream);
+    case 9: return launch_chunk<9, GRADS>(args, groups, smem, stream);
+    case 18: return launch_chunk<18, GRADS>(args, groups, smem, stream);
+    default: return launch_chunk<0, GRADS>(args, groups, smem, stream);
+  }
+}
+
+static int run_chunk_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
+                          int* num_partials, bool* losses_done, bool* exchange_done) {
+  int S = 0, C = 0;
+  if (!chunk_shape(p, &S, &C))
+    return fail(VTR_ERR_UNSUPPORTED, "chunk kernel: needs B <= %d and T <= %d steps per chunk x %d chunks",
+                kChunkMaxColumns, kChunkMaxSteps, kChunkMaxChunks);
+  const int groups = column_tiles(p->B);
+  ChunkArgs args;
+  fill_args(args.f, p, partials);
+  const bool rows_aligned = (static_cast<size_t>(p->B) * p->A) % 4 == 0;
+  args.f.tma_in_ok = rows_aligned && aligned(args.f.blog, 16) && aligned(args.f.tlog, 16);
+  args.f.tma_out_ok = rows_aligned && aligned(args.f.d_logits, 16);
+  args.steps = S, args.chunks = C;
+  *num_partials = groups * C;  // one partial per CTA
+  if (int rc = fill_finish(&args.fin, p, partials != nullptr, groups * C, groups * C, stream, losses_done,
+                           exchange_done))
+    return rc;
+#ifdef VTR_CHUNK_TRACE
+  args.trace = nullptr;
+  if (const char* v = getenv("VTR_CHUNK_TRACE_PTR")) args.trace = reinterpret_cast<unsigned long long*>(strtoull(v, nullptr, 16));
+#endif
+  const size_t smem = chunk_smem_bytes(p->A, S);
+  return p->d_target_logits ? dispatch_chunk<true>(args, groups, smem, stream)
+                            : dispatch_chunk<false>(args, groups, smem, stream);
+}
+
+// VTR_PATH_AUTO takes K2 (a CTA per column, a lane per time step) where
+// lane-per-column kernels would leave most lanes idle, and for long unrolls of
+// small batches that K5 cannot split (T beyond its steps x chunks): its
+// threads read their rows straight from global memory, 72-byte pieces 2 MB
+// apart, which is fine for a few hundred columns and slower than K1b's ring
+// beyond (measured at T=100 A=18: B=256 14 us vs 25 us, B=512 20 us vs 25 us,
+// B=1024 29 us vs 26 us, B=2048 50 us vs 23 us).
+constexpr int kItemTinyColumns = 16;
+constexpr int kItemAutoColumns = 512;
+static bool item_kernel_applies(const vtr_fused_params* p, int max_columns) {
+  return p->T <= kItemMaxSteps && specialised_actions(p->A) && p->B <= max_columns;
+}
+
+// VTR_PATH_AUTO takes K5 while its CTAs (column groups x chunks) fit the GPU in
+// little more than one wave: there every SM gets work however few column
+// groups there are, and the launch costs one CTA's latency.  A CTA does load,
+// compute, store one after the other, so with several waves the 32-column
+// tiles, whose ring keeps loads ahead of the arithmetic, are faster (measured
+// on B200, T=100 A=18: B=1024 12.3 vs 22.6 us, 2048 19.6 vs 23.9, 3072 25.1 vs
+// 24.6, 4096 31.5 vs 24.6; T=20: 4096 10.3 vs 11.6, 8192 14.1 vs 13.9, 16384
+// 24.7 vs 20.6).
+static bool chunk_kernel_applies(const vtr_fused_params* p) {
+  int S = 0, C = 0;
+  if (!chunk_shape(p, &S, &C) || C > 8 || getenv("VTR_NO_CHUNK")) return false;
+  DeviceInfo dev;
+  if (device_info(&dev) != VTR_OK) return false;
+  // CTAs an SM holds: registers (32 for a compiled-in A <= 9, else 48), shared
+  // memory, threads.
+  const int regs = (specialised_actions(p->A) && p->A <= 9) ? 32 : 48;
+  int per_sm = 65536 / (regs * 32 * S);
+  per_sm = min(per_sm, static_cast<int>(dev.smem_per_sm / (chunk_smem_bytes(p->A, S) + 1024)));
+  per_sm = min(per_sm, 2048 / (32 * S));
+  if (per_sm < 1) return false;
+  const long ctas = static_cast<long>(column_tiles(p->B)) * C;
+  return 4 * ctas <= 5L * per_sm * dev.sm_count;
+}
+
+template <int A_CT, bool GRADS>
+static int launch_item(const ItemArgs& args, cudaStream_t stream) {
+  const int threads = ((args.f.T + 31) / 32) * 32;
+  if (g_plan.dry_run) {
+    record_plan("fused_item_kernel<A=%d,%s> grid=%d threads=%d%s%s; ", A_CT, GRADS ? "grads" : "fwd", args.f.B,
+                threads, args.fin.ticket ? " + in-kernel final reduction" : "",
+                args.fin.ex_world > 0 ? (args.fin.ex_sums ? " + peer publish + collect" : " + peer publish")
+                                      : "");
+    return VTR_OK;
+  }
+  fused_item_kernel<A_CT, GRADS><<<args.f.B, threads, 0, stream>>>(args);
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;
 }
 
 template <bool GRADS>
-static int dispatch_item(const FusedArgs& args, cudaStream_t stream) {
-  switch (args.A) {
+static int dispatch_item(const ItemArgs& args, cudaStream_t stream) {
+  switch (args.f.A) {
     case 3: return launch_item<3, GRADS>(args, stream);
     case 4: return launch_item<4, GRADS>(args, stream);
     case 6: return launch_item<6, GRADS>(args, stream);
     case 9: return launch_item<9, GRADS>(args, stream);
     case 18: return launch_item<18, GRADS>(args, stream);
-    default: return fail(VTR_ERR_UNSUPPORTED, "item kernel: A=%d is not a compiled-in size", args.A);
+    default: return fail(VTR_ERR_UNSUPPORTED, "item kernel: A=%d is not a compiled-in size", args.f.A);
   }
 }
 
+// The last CTA of K2 sums one partial per column with at most 256 threads:
+// fine for the small batches this kernel is meant for, K3 beyond.
+constexpr int kItemFinishColumns = 1024;
+
 static int run_item_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
-                         int* num_partials) {
+                         int* num_partials, bool* losses_done, bool* exchange_done) {
   if (p->T > kItemMaxSteps || p->B > kItemMaxColumns)
     return fail(VTR_ERR_UNSUPPORTED, "item kernel: needs T <= %d and B <= %d", kItemMaxSteps,
                 kItemMaxColumns);
-  FusedArgs a;
-  fill_args(a, p, partials);
+  ItemArgs a;
+  fill_args(a.f, p, partials);
   *num_partials = p->B;  // one partial per column
+  if (int rc = fill_finish(&a.fin, p, partials != nullptr && p->B <= kItemFinishColumns, p->B, p->B, stream,
+                           losses_done, exchange_done))
+    return rc;
   return p->d_target_logits ? dispatch_item<true>(a, stream) : dispatch_item<false>(a, stream);
 }
 
+// The last CTA of K1a/K1b sums one partial per tile with one warp: fine up to
+// a thousand tiles, K3 beyond.
+constexpr int kTileFinishTiles = 1024;
+
 static int run_column_path(const vtr_fused_params* p, double* partials, cudaStream_t stream,
-                           int* num_partials) {
+                           int* num_partials, bool* losses_done, bool* exchange_done) {
   DeviceInfo dev;
   if (int rc = device_info(&dev)) return rc;
   const int tiles = column_tiles(p->B);
   const bool grads = p->d_target_logits != nullptr;
   *num_partials = tiles;
 
-  FusedArgs a;
+  TileArgs targs;
+  FusedArgs& a = targs.f;
   fill_args(a, p, partials);
+  if (int rc = fill_finish(&targs.fin, p, partials != nullptr && tiles <= kTileFinishTiles, tiles, tiles,
+                           stream, losses_done, exchange_done))
+    return rc;
 
   // A row of the tile for step t starts at element (t*B + 32*tile)*A; TMA bulk
   // copies need 16-byte alignment of every such address.
@@ -424,8 +676,52 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   a.depth = static_cast<int>(depth);
   a.slot_floats = static_cast<int>(slot_bytes / sizeof(float));
 
-  return grads ? dispatch_tiles<true>(a, tiles, warps, smem, stream)
-               : dispatch_tiles<false>(a, tiles, warps, smem, stream);
+  return grads ? dispatch_tiles<true>(targs, tiles, warps, smem, stream)
+               : dispatch_tiles<false>(targs, tiles, warps, smem, stream);
+}
+
+// Which kernels a call may run, in the order they are tried: K1c if wanted,
+// then `second`; under VTR_PATH_AUTO a kernel that turns the shape down
+// (VTR_ERR_UNSUPPORTED) hands over to the 32-column-tile kernels, which take
+// everything.
+enum SecondChoice { kSecondColumn, kSecondItem, kSecondChunk };
+struct KernelChoice {
+  bool sm_tile;
+  SecondChoice second;
+};
+
+static KernelChoice choose_kernels(const vtr_fused_params* p) {
+  KernelChoice c;
+  c.sm_tile = p->path == VTR_PATH_SM_TILE || (p->path == VTR_PATH_AUTO && sm_tile_preferred(p));
+  c.second = kSecondColumn;
+  if (p->path == VTR_PATH_ITEM) c.second = kSecondItem;
+  else if (p->path == VTR_PATH_CHUNK) c.second = kSecondChunk;
+  else if (p->path == VTR_PATH_AUTO) {
+    if (item_kernel_applies(p, kItemTinyColumns)) c.second = kSecondItem;
+    else if (chunk_kernel_applies(p)) c.second = kSecondChunk;
+    else if (item_kernel_applies(p, kItemAutoColumns)) c.second = kSecondItem;
+  }
+  return c;
+}
+
+// Loss partials (double[3] each) the kernels of `c` may write: one per
+// 4-column granule (K1c), per column (K2), per CTA (K5) or per 32-column tile
+// (K1a/K1b); the largest of those the call can end up running.
+static size_t partials_needed(const vtr_fused_params* p, const KernelChoice& c) {
+  const size_t tiles = static_cast<size_t>(column_tiles(p->B));
+  size_t need = 0;
+  if (c.sm_tile) need = static_cast<size_t>(p->B / 4);
+  if (p->path != VTR_PATH_SM_TILE) {
+    size_t second = tiles;
+    if (c.second == kSecondItem) second = static_cast<size_t>(p->B);
+    if (c.second == kSecondChunk) {
+      int S = 0, C = 1;
+      if (chunk_shape(p, &S, &C)) second = tiles * C;  // else the call fails or falls back
+    }
+    if (second > need) need = second;
+    if (p->path == VTR_PATH_AUTO && tiles > need) need = tiles;
+  }
+  return need;
 }
 
 }  // namespace vtr
@@ -433,10 +729,14 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
 extern "C" size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A) {
   if (T <= 0 || B <= 0 || A <= 0) return 0;
   // header + one double[3] per 32-column tile (K1a/K1b), per 4-column granule
-  // (K1c) or per column (K2, which only runs below kItemMaxColumns columns)
-  size_t partials = static_cast<size_t>(vtr::column_tiles(B));
+  // (K1c), per column (K2, which only runs below kItemMaxColumns columns) or
+  // per CTA (K5: at most kChunkMaxChunks per tile, below kChunkMaxColumns)
+  const size_t tiles = static_cast<size_t>(vtr::column_tiles(B));
+  size_t partials = tiles;
   if (static_cast<size_t>(B / 4) > partials) partials = B / 4;
   if (B <= vtr::kItemMaxColumns && static_cast<size_t>(B) > partials) partials = B;
+  if (B <= vtr::kChunkMaxColumns && tiles * vtr::kChunkMaxChunks > partials)
+    partials = tiles * vtr::kChunkMaxChunks;
   return vtr::kWorkspaceHeaderBytes + partials * 3 * sizeof(double);
 }
 
@@ -470,7 +770,7 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     return fail(VTR_ERR_INVALID_ARGUMENT, "one of discounts / done must be given");
   if (p->reward_clip_mode < VTR_REWARD_CLIP_NONE || p->reward_clip_mode > VTR_REWARD_CLIP_SOFT_ASYMMETRIC)
     return fail(VTR_ERR_UNSUPPORTED, "unknown reward_clip_mode %d", p->reward_clip_mode);
-  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_ITEM)
+  if (p->path < VTR_PATH_AUTO || p->path > VTR_PATH_CHUNK)
     return fail(VTR_ERR_UNSUPPORTED, "unknown path %d", p->path);
   if ((p->d_values != nullptr) && !p->d_target_logits)
     return fail(VTR_ERR_INVALID_ARGUMENT, "d_values requires d_target_logits");
@@ -490,20 +790,24 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
       return fail(VTR_ERR_INVALID_ARGUMENT, "bad exchange rank/world %d/%d", p->exchange_rank,
                   p->exchange_world);
     if (p->exchange_seq == 0) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_seq must start at 1");
+    if (p->exchange_lag > 1) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_lag must be 0 or 1");
     if (!vtr::aligned(p->exchange_sums, 4)) return fail(VTR_ERR_MISALIGNED, "exchange_sums is not 4-byte aligned");
     for (int r = 0; r < p->exchange_world; ++r)
       if (!p->exchange_peer_buffers[r])
         return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_peer_buffers[%d] is NULL", r);
   }
+  if (p->path == VTR_PATH_SM_TILE && !vtr::sm_tile_eligible(p))
+    return fail(VTR_ERR_UNSUPPORTED,
+                "VTR_PATH_SM_TILE needs B %% 4 == 0 and 16-byte aligned tensors");
+  if (p->path == VTR_PATH_ITEM && p->B > vtr::kItemMaxColumns)
+    return fail(VTR_ERR_UNSUPPORTED, "VTR_PATH_ITEM needs B <= %d", vtr::kItemMaxColumns);
+  const vtr::KernelChoice choice = vtr::choose_kernels(p);
   const bool want_losses = p->losses || p->losses_f64;
   double* partials = nullptr;
   if (want_losses) {
-    // K1a/K1b write one partial per 32-column tile, K1c one per 4-column granule.
-    const size_t need = p->path == VTR_PATH_COLUMN
-                            ? vtr::kWorkspaceHeaderBytes + vtr::column_tiles(p->B) * 3 * sizeof(double)
-                            : vtr_fused_workspace_bytes(p->T, p->B, p->A);
-    if (p->path == VTR_PATH_ITEM && p->B > vtr::kItemMaxColumns)
-      return fail(VTR_ERR_UNSUPPORTED, "VTR_PATH_ITEM needs B <= %d", vtr::kItemMaxColumns);
+    // What the kernels this call may run really write; never more than
+    // vtr_fused_workspace_bytes() says.
+    const size_t need = vtr::kWorkspaceHeaderBytes + vtr::partials_needed(p, choice) * 3 * sizeof(double);
     if (!workspace || workspace_bytes < need)
       return fail(VTR_ERR_WORKSPACE, "workspace of %zu bytes needed, %zu given", need, workspace_bytes);
     if (!vtr::aligned(workspace, 8)) return fail(VTR_ERR_MISALIGNED, "workspace is not 8-byte aligned");
@@ -512,21 +816,24 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   int num_partials = 0;
   int rc = VTR_ERR_UNSUPPORTED;
-  const bool want_sm_tile = p->path == VTR_PATH_SM_TILE ||
-                            (p->path == VTR_PATH_AUTO && vtr::sm_tile_preferred(p));
-  if (p->path == VTR_PATH_SM_TILE && !vtr::sm_tile_eligible(p))
-    return fail(VTR_ERR_UNSUPPORTED,
-                "VTR_PATH_SM_TILE needs B %% 4 == 0 and 16-byte aligned tensors");
+  const bool want_sm_tile = choice.sm_tile;
   bool losses_done = false, exchange_done = false;
+  const vtr::SecondChoice second = choice.second;
   if (want_sm_tile)
     rc = vtr::run_sm_tile_path(p, want_losses ? workspace : nullptr, partials, s, &num_partials,
                                &losses_done, &exchange_done);
   if (rc == VTR_ERR_UNSUPPORTED && p->path != VTR_PATH_SM_TILE) {
     losses_done = exchange_done = false;
-    if (p->path == VTR_PATH_ITEM || (p->path == VTR_PATH_AUTO && vtr::item_kernel_applies(p)))
-      rc = vtr::run_item_path(p, partials, s, &num_partials);
+    if (second == vtr::kSecondItem)
+      rc = vtr::run_item_path(p, partials, s, &num_partials, &losses_done, &exchange_done);
+    else if (second == vtr::kSecondChunk)
+      rc = vtr::run_chunk_path(p, partials, s, &num_partials, &losses_done, &exchange_done);
     else
-      rc = vtr::run_column_path(p, partials, s, &num_partials);
+      rc = vtr::run_column_path(p, partials, s, &num_partials, &losses_done, &exchange_done);
+    // a cluster the device cannot schedule: the 32-column-tile kernels always run
+    if (rc == VTR_ERR_UNSUPPORTED && second != vtr::kSecondColumn && p->path == VTR_PATH_AUTO) {
+      rc = vtr::run_column_path(p, partials, s, &num_partials, &losses_done, &exchange_done);
+    }
   }
   if (rc) return rc;
   if (want_losses && !losses_done) {
@@ -537,14 +844,15 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   if (want_exchange && !exchange_done) {
     if (vtr::g_plan.dry_run) {
       vtr::record_plan("exchange_publish_kernel grid=1; ");
-      if (p->exchange_sums) vtr::record_plan("exchange_collect_kernel grid=1; ");
+      if (p->exchange_sums && p->exchange_seq > p->exchange_lag)
+        vtr::record_plan("exchange_collect_kernel grid=1; ");
       return VTR_OK;
     }
     rc = vtr_exchange_publish_f32(p->losses, 4, p->exchange_peer_buffers, p->exchange_rank,
                                   p->exchange_world, p->exchange_seq, stream);
-    if (rc || !p->exchange_sums) return rc;
+    if (rc || !p->exchange_sums || p->exchange_seq <= p->exchange_lag) return rc;
     return vtr_exchange_collect_f32(p->exchange_peer_buffers[p->exchange_rank], 4, p->exchange_world,
-                                    p->exchange_seq, p->exchange_sums, stream);
+                                    p->exchange_seq - p->exchange_lag, p->exchange_sums, stream);
   }
   return VTR_OK;
 }
@@ -616,20 +924,33 @@ extern "C" int vtr_from_logits_fused_noalloc_f32(const vtr_fused_params* p, void
                      "vtr_from_logits_fused_noalloc_f32: B=%d is above VTR_NOALLOC_MAX_B=%d, the most "
                      "the built-in scratch holds; use vtr_from_logits_fused_f32 with your own workspace",
                      p->B, VTR_NOALLOC_MAX_B);
+  if (!p->losses && !p->losses_f64)  // no losses, no partials: the scratch is not touched
+    return vtr_from_logits_fused_f32(p, nullptr, 0, stream);
+  if (p->T <= 0 || p->B <= 0 || p->A <= 0 || p->path < VTR_PATH_AUTO || p->path > VTR_PATH_CHUNK)
+    return vtr_from_logits_fused_f32(p, nullptr, 0, stream);  // reports the bad argument
   double* scratch = nullptr;
   if (int rc = vtr::noalloc_scratch(&scratch)) return rc;
-  // The scratch holds one partial per 32-column tile of the largest batch.  The
-  // other kernels write more partials per column, so they are only eligible
-  // while their workspace still fits; beyond that this entry point takes the
-  // 32-column-tile kernels.  The partials never have to start at zero: the
-  // first stage writes every one the second stage reads, so whatever an
-  // earlier call left behind is overwritten or never looked at.  The per-SM
-  // kernel keeps a cursor in the scratch header; the library zeroes that
-  // itself before every launch that uses it.
+  // The scratch holds one partial per 32-column tile of the largest batch.
+  // The other kernels write more partials per column, so the automatic choice
+  // keeps them only while what they write still fits, and takes the 32-column
+  // tiles beyond that.  The partials never have to start at zero: the first
+  // stage writes every one the second stage reads, so whatever an earlier
+  // call left behind is overwritten or never looked at.  The per-SM kernel
+  // keeps a cursor in the scratch header; the library zeroes that itself
+  // before every launch that uses it.
   const size_t scratch_bytes = sizeof(double) * vtr::kNoAllocDoubles;
   vtr_fused_params q = *p;
-  if (q.path == VTR_PATH_AUTO && vtr_fused_workspace_bytes(q.T, q.B, q.A) > scratch_bytes)
+  const size_t need = vtr::kWorkspaceHeaderBytes +
+                      vtr::partials_needed(&q, vtr::choose_kernels(&q)) * 3 * sizeof(double);
+  if (need > scratch_bytes) {
+    if (q.path != VTR_PATH_AUTO)
+      return vtr::fail(VTR_ERR_UNSUPPORTED,
+                       "vtr_from_logits_fused_noalloc_f32: the kernel asked for with path=%d writes %zu "
+                       "bytes of loss partials at B=%d, the built-in scratch holds %zu; leave the "
+                       "choice to the library (VTR_PATH_AUTO) or pass a workspace to "
+                       "vtr_from_logits_fused_f32",
+                       q.path, need, q.B, scratch_bytes);
     q.path = VTR_PATH_COLUMN;
+  }
   return vtr_from_logits_fused_f32(&q, scratch, scratch_bytes, stream);
 }
-

@@ -101,6 +101,45 @@ __device__ __forceinline__ float row_entropy(float (&x)[N], const float (&e)[N],
   return __fmul_rn(-inv_sum, __fadd_rn(h0, h1));
 }
 
+// Target row for kernels that do not keep the terms e_i (K5): the statistics
+// and dot = sum_i e_i (x_i - m), from which H = -sum p_i log p_i
+// = ln_sum - dot / sum (log p_i = (x_i - m) - ln_sum).  The terms and their
+// sum are formed exactly as in row_stats(), so the action log-probs carry the
+// same bits as in the other kernels.
+template <int N>
+__device__ __forceinline__ RowStats row_stats_dot(const float (&x)[N], float& dot) {
+  RowStats r;
+  r.m = row_max(x);
+  const ExpOffset off(r.m);
+  float s0 = 0.0f, s1 = 0.0f, d0 = 0.0f, d1 = 0.0f;
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    const float e = off.term(x[i]);
+    const float c = __fsub_rn(x[i], r.m);
+    if (i & 1) s1 = __fadd_rn(s1, e), d1 = __fmaf_rn(e, c, d1);
+    else s0 = __fadd_rn(s0, e), d0 = __fmaf_rn(e, c, d0);
+  }
+  r.sum = __fadd_rn(s0, s1);
+  r.ln_sum = off.ln_sum(r.sum);
+  dot = __fadd_rn(d0, d1);
+  return r;
+}
+__device__ __forceinline__ float entropy_from_dot(const RowStats& r, float dot, float inv_sum) {
+  return __fsub_rn(r.ln_sum, __fmul_rn(dot, inv_sum));
+}
+
+// x <- the gradient row but for the -onehot(a) pg_adv term, e_i (ka lp_i + kb),
+// with the terms recomputed from the logits (same bits as row_stats()).
+template <int N>
+__device__ __forceinline__ void row_gradient_from_logits(float (&x)[N], const RowStats& r, float ka,
+                                                         float kb) {
+  const ExpOffset off(r.m);
+  const float lse = __fadd_rn(r.m, r.ln_sum);
+#pragma unroll
+  for (int i = 0; i < N; ++i)
+    x[i] = __fmul_rn(off.term(x[i]), __fmaf_rn(ka, __fsub_rn(x[i], lse), kb));
+}
+
 // e <- p_i (entropy_cost lp_i + k) = e_i (ka lp_i + kb) with ka = ec/sum,
 // kb = k/sum, k = pg_adv + entropy_cost H: the gradient row but for the
 // -onehot(a) pg_adv term.

@@ -23,6 +23,8 @@
 // exist once per box instead of once per GPU.
 #include <math.h>
 
+#include <atomic>
+
 #include "common.h"
 #include "exchange.cuh"
 
@@ -82,12 +84,17 @@ __global__ void __launch_bounds__(256) rmsprop_kernel(float* __restrict__ var, f
 // zeroed once): [r] = rank r's gradient is final for step seq; [16 + r] =
 // rank r's slice of the parameters is in place for step seq; [32] = blocks of
 // this launch that are done (local ticket); [33] = sticky status, non-zero
-// after a wait timed out.
+// once a step failed; [34] = this launch's go / no-go, decided once by block 0
+// and read by every block.  A flag word holds seq, or seq | kSyncFailed when
+// its writer gave the step up (a peer did not show up in time): whoever waits
+// on it then gives up too, at once, instead of using half-finished data.
 // ---------------------------------------------------------------------------
 constexpr int kSyncGradFlags = 0;
 constexpr int kSyncDoneFlags = 16;
 constexpr int kSyncTicket = 32;
 constexpr int kSyncStatus = 33;
+constexpr int kSyncGo = 34;
+constexpr uint32_t kSyncFailed = 0x80000000u;  // seq stays below 2^31
 
 struct RmsShardArgs {
   PeerBuffers var;   // every rank's full parameter buffer, as mapped here
@@ -100,13 +107,15 @@ struct RmsShardArgs {
   uint32_t seq;
   RmsHyper h;
   unsigned long long timeout_ns;
+  uint32_t* host_status;  // pinned host word the kernel sets to seq on failure, or null
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// Spins until *flag == want; false after timeout_ns (a peer is missing).
+// Spins until *flag carries step `want`: true if its writer went ahead, false
+// if it gave the step up or nothing came within timeout_ns (a peer is missing).
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t want, unsigned long long timeout_ns) {
   unsigned long long t0, now;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -114,9 +123,28 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t want, u
     uint32_t v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
     if (v == want) return true;
+    if (v == (want | kSyncFailed)) return false;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
     if (now - t0 > timeout_ns) return false;
     __nanosleep(64);
+  }
+}
+
+// This rank gives step `seq` up: sticky status here, the host word if there is
+// one, and the failure marker in both flags of every peer, so that a peer
+// that is waiting for this rank - or turns up later - gives up as well.
+__device__ __forceinline__ void give_up(const RmsShardArgs& a, uint32_t* my_sync, int tid) {
+  if (tid < a.world) {
+    uint32_t* peer = reinterpret_cast<uint32_t*>(a.sync.p[tid]);
+    st_release_sys(peer + kSyncGradFlags + a.rank, a.seq | kSyncFailed);
+    st_release_sys(peer + kSyncDoneFlags + a.rank, a.seq | kSyncFailed);
+  }
+  if (tid == 0) {
+    my_sync[kSyncStatus] = 1u;
+    if (a.host_status) {
+      *reinterpret_cast<volatile uint32_t*>(a.host_status) = a.seq;
+      __threadfence_system();
+    }
   }
 }
 
@@ -137,15 +165,25 @@ __global__ void __launch_bounds__(256) rmsprop_allreduce_kernel(const __grid_con
 
   // ---- 0: gradients are final everywhere ----
   // This rank's gradient was written by earlier work on this stream, so it is
-  // complete when this kernel starts; block 0 says so to every peer.
-  if (blockIdx.x == 0 && tid < a.world) {
-    __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(a.sync.p[tid]) + kSyncGradFlags + a.rank, a.seq);
+  // complete when this kernel starts; block 0 says so to every peer, waits for
+  // theirs and decides for the whole grid: every block takes the same branch,
+  // so a slice is updated completely or not at all.
+  if (blockIdx.x == 0) {
+    if (tid < a.world) {
+      __threadfence_system();
+      st_release_sys(reinterpret_cast<uint32_t*>(a.sync.p[tid]) + kSyncGradFlags + a.rank, a.seq);
+    }
+    if (tid == 0) sh_ok = 1;
+    __syncthreads();
+    if (tid < a.world && !wait_flag(my_sync + kSyncGradFlags + tid, a.seq, a.timeout_ns)) sh_ok = 0;
+    __syncthreads();
+    if (!sh_ok) give_up(a, my_sync, tid);
+    if (tid == 0) st_release_sys(my_sync + kSyncGo, sh_ok ? a.seq : (a.seq | kSyncFailed));
+  } else {
+    // block 0 is resident before any other block starts; its wait is bounded
+    if (tid == 0) sh_ok = wait_flag(my_sync + kSyncGo, a.seq, 4 * a.timeout_ns) ? 1 : 0;
+    __syncthreads();
   }
-  if (tid == 0) sh_ok = 1;
-  __syncthreads();
-  if (tid < a.world && !wait_flag(my_sync + kSyncGradFlags + tid, a.seq, a.timeout_ns)) sh_ok = 0;
-  __syncthreads();
   const bool ok = sh_ok != 0;
 
   // ---- 1: reduce-scatter + update + all-gather of this rank's slice ----
@@ -208,16 +246,20 @@ __global__ void __launch_bounds__(256) rmsprop_allreduce_kernel(const __grid_con
   }
   __syncthreads();
   if (!sh_last) return;
+  if (tid == 0) my_sync[kSyncTicket] = 0u;  // ready for the next launch
+  if (!ok) return;                          // given up in phase 0: the peers were told there
   __threadfence_system();  // the other blocks' stores are ordered before the flag below
-  bool done_ok = true;
+  if (tid == 0) sh_ok = 1;
+  __syncthreads();
   if (tid < a.world) {
     st_release_sys(reinterpret_cast<uint32_t*>(a.sync.p[tid]) + kSyncDoneFlags + a.rank, a.seq);
     // Until every peer has said the same, some of them may still be reading
-    // this rank's gradient or writing into its parameters.
-    done_ok = wait_flag(my_sync + kSyncDoneFlags + tid, a.seq, a.timeout_ns);
+    // this rank's gradient or writing into its parameters.  A peer that gave
+    // the step up (or never came) leaves the parameters out of step: flagged.
+    if (!wait_flag(my_sync + kSyncDoneFlags + tid, a.seq, a.timeout_ns)) sh_ok = 0;
   }
-  if (!ok || !done_ok) my_sync[kSyncStatus] = 1u;
-  if (tid == 0) my_sync[kSyncTicket] = 0u;  // ready for the next launch
+  __syncthreads();
+  if (!sh_ok) give_up(a, my_sync, tid);
 }
 
 }  // namespace vtr
@@ -282,15 +324,29 @@ extern "C" int vtr_rmsprop_slice(int64_t n, int32_t world, int32_t rank, int64_t
 
 extern "C" size_t vtr_rmsprop_sync_bytes(void) { return 64 * sizeof(uint32_t); }
 
+// How long a rank waits for its peers before it gives a step up.  Ranks of a
+// learner drift apart by far more than a kernel's length now and then (an
+// actor batch arriving late, a checkpoint being written), so the default is
+// generous; it only has to keep a dead peer from hanging the GPU for good.
+static std::atomic<unsigned long long> g_peer_timeout_ns{20000000000ull};  // 20 s
+
+extern "C" void vtr_set_peer_timeout_ms(uint64_t milliseconds) {
+  if (milliseconds == 0) milliseconds = 1;
+  g_peer_timeout_ns.store(static_cast<unsigned long long>(milliseconds) * 1000000ull);
+}
+extern "C" uint64_t vtr_get_peer_timeout_ms(void) { return g_peer_timeout_ns.load() / 1000000ull; }
+
 extern "C" int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* grad_peers,
                                          void* const* sync_peers, float* ms_slice, float* mom_slice,
                                          int64_t n, int32_t rank, int32_t world, uint32_t seq,
                                          float learning_rate, float decay, float momentum,
-                                         float epsilon, void* stream) {
+                                         float epsilon, uint32_t* host_status, void* stream) {
   if (n <= 0) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_rmsprop_allreduce: n must be positive");
   if (world <= 0 || world > VTR_EXCHANGE_MAX_RANKS || rank < 0 || rank >= world)
     return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_rmsprop_allreduce: bad rank/world %d/%d", rank, world);
-  if (seq == 0) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_rmsprop_allreduce: seq must start at 1");
+  if (seq == 0 || seq >= vtr::kSyncFailed)
+    return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_rmsprop_allreduce: seq must be in [1, 2^31)");
+  if (!vtr::aligned(host_status, 4)) return fail(VTR_ERR_MISALIGNED, "vtr_rmsprop_allreduce: host_status");
   if (int rc = check_hyper("vtr_rmsprop_allreduce", decay, momentum, epsilon)) return rc;
   vtr::RmsShardArgs a;
   if (int rc = vtr::fill_peer_buffers(&a.var, var_peers, world)) return rc;
@@ -313,7 +369,8 @@ extern "C" int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* gr
   a.n = n, a.lo = lo, a.hi = hi;
   a.rank = rank, a.world = world, a.seq = seq;
   a.h = {learning_rate, 1.0f - decay, momentum, epsilon};
-  a.timeout_ns = vtr::kExchangeTimeoutNs;
+  a.timeout_ns = g_peer_timeout_ns.load();
+  a.host_status = host_status;
   // Every rank launches, even one whose slice is empty: its peers wait for its flags.
   const int unroll = world <= 2 ? 4 : world <= 4 ? 2 : 1;
   const int blocks = blocks_for((((hi - lo) >> 2) + unroll - 1) / unroll);

@@ -105,20 +105,29 @@ class LossExchange(object):
     torch.cuda.synchronize(self.device)
     dist.barrier(self.group)   # every buffer is zeroed before anyone publishes
 
-  def attach(self, params, sums=None):
+  def attach(self, params, sums=None, lag=0):
     """Makes the next fused call do the exchange itself: fills the exchange_*
     fields of a `_lib.FusedParams` with this exchange's buffers and the next
-    sequence number.  The per-SM kernel then stores the four scalars into the
-    peers from the tile that finishes the loss reduction.  With `sums` (a
-    float32 CUDA tensor of 4) the same tile also waits for the peers' scalars
-    and writes the sum over ranks there, and the step needs no further call;
-    without it follow the fused call with `collect()` on the same stream.
+    sequence number.  The kernel then stores the four scalars into the peers
+    from the CTA that finishes the loss reduction.  With `sums` (a float32
+    CUDA tensor of 4) the same CTA also writes a sum over ranks there:
+
+      lag=0  this step's sums: the launch ends only when the slowest rank has
+             published, so every step pays the rendezvous;
+      lag=1  the previous step's sums, which are normally in this rank's buffer
+             already: no rank waits for another (nothing is written on the
+             first step; fetch the last step's sums with `collect()`).
+
+    Without `sums`, follow the fused call with `collect()` on the same stream.
     Every rank must make the same choice, once per step."""
+    if lag not in (0, 1):
+      raise ValueError('lag must be 0 or 1')
     self.seq += 1
     params.exchange_peer_buffers = ctypes.cast(self._peer_ptrs,
                                                ctypes.POINTER(ctypes.c_void_p))
     params.exchange_rank, params.exchange_world = self.rank, self.world
     params.exchange_seq = self.seq
+    params.exchange_lag = lag
     if sums is not None:
       if (sums.dtype != torch.float32 or sums.numel() < 4 or
           not sums.is_contiguous() or sums.device != self.device):
@@ -129,7 +138,8 @@ class LossExchange(object):
     return self.seq
 
   def collect(self, n=4):
-    """Sum over ranks of what the ranks published for the current step."""
+    """Sum over ranks of what the ranks published for the current step (waits
+    on the device until every rank has)."""
     out = torch.empty(n, dtype=torch.float32, device=self.device)
     stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
     with torch.cuda.device(self.device):

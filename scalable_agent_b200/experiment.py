@@ -84,7 +84,8 @@ def compute_vtrace_loss(
       `rewards` inside the kernel (experiment.py:377-382).
     done: optional bool [T, B]; discounts = (~done) * discounting (:384).
     return_aux: also materialise log_rhos and the two action log-prob fields.
-    path: 'auto', 'column' or 'sm_tile' (kernel choice).
+    path: 'auto', 'column', 'sm_tile', 'item' or 'chunk' (kernel choice; see
+      DESIGN.md).
 
   Returns:
     VTraceLossReturns(total_loss, policy_gradient_loss, baseline_loss,

@@ -107,6 +107,9 @@ class RMSPropOptimizer(object):
       self.sync = symm_mem.empty(self.lib.vtr_rmsprop_sync_bytes() // 4,
                                  dtype=torch.int32, device=dev)
       self.flat.zero_(), self.flat_grad.zero_(), self.sync.zero_()
+      # a word in pinned host memory the kernel writes when it gives a step up:
+      # step() looks at it without synchronising the device
+      self._host_status = torch.zeros(1, dtype=torch.int32, pin_memory=True)
       self._peers = []
       for buf in (self.flat, self.flat_grad, self.sync):
         handle = symm_mem.rendezvous(buf, group)
@@ -150,6 +153,11 @@ class RMSPropOptimizer(object):
         raise RuntimeError(
             'RMSPropOptimizer: a parameter\'s .grad no longer points into the '
             'flat gradient buffer (use optimizer.zero_grad(), not set_to_none)')
+    if self.group is not None and int(self._host_status[0]) != 0:
+      raise RuntimeError(
+          'RMSPropOptimizer: step %d was given up because a peer did not reach '
+          'the optimiser step within %d ms; parameters are no longer in sync'
+          % (int(self._host_status[0]), self.lib.vtr_get_peer_timeout_ms()))
     lr = self.current_learning_rate()
     self.steps += 1
     stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -166,12 +174,14 @@ class RMSPropOptimizer(object):
         rc = self.lib.vtr_rmsprop_allreduce_f32(
             var_peers, grad_peers, sync_peers, self.ms.data_ptr(), mom, self.n,
             self.rank, self.world, self.steps, lr, self.decay, self.momentum,
-            self.epsilon, stream)
+            self.epsilon, self._host_status.data_ptr(), stream)
         _lib.check(rc, 'vtr_rmsprop_allreduce_f32')
 
   def check_peers(self):
-    """Raises if a peer ever failed to show up within the kernel's time-out
-    (synchronises the device; for tests and health checks, not every step)."""
+    """Raises if a step was ever given up because a peer did not show up within
+    the time-out (synchronises the device; `step()` itself checks the previous
+    steps through a pinned host word, without synchronising)."""
     if self.group is not None and int(self.sync[33].item()) != 0:
       raise RuntimeError('RMSPropOptimizer: a peer did not reach the optimiser '
-                         'step within 2 s; parameters are no longer in sync')
+                         'step within %d ms; parameters are no longer in sync'
+                         % self.lib.vtr_get_peer_timeout_ms())

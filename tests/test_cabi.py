@@ -33,7 +33,8 @@ def test_version_and_sizes():
   lib = _lib.load()
   assert lib.vtr_version() == 100
   assert lib.vtr_fused_workspace_bytes(100, 32768, 18) == 8192 + 8192 * 24
-  assert lib.vtr_fused_workspace_bytes(5, 2, 3) == 8192 + 2 * 24   # K2: one partial per column
+  assert lib.vtr_fused_workspace_bytes(5, 2, 3) == 8192 + 16 * 24  # K5: up to 16 CTAs per 32 columns
+  assert lib.vtr_fused_workspace_bytes(5, 700, 3) == 8192 + 700 * 24  # K2: one partial per column
   assert lib.vtr_fused_workspace_bytes(0, 4, 4) == 0
   assert lib.vtr_loss_workspace_bytes(1) == 8
   assert lib.vtr_loss_workspace_bytes(0) == 0

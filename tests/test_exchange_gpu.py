@@ -63,8 +63,10 @@ def test_loss_exchange_two_ranks(tmp_path):
 # ---------------------------------------------------------------------------
 KEYS = ('behaviour_policy_logits', 'target_policy_logits', 'actions',
         'discounts', 'rewards', 'values', 'bootstrap_value')
-# (T, B, A): the per-SM kernel publishes from inside; the small one appends a launch
-FUSED_SHAPES = [(32, 64 * 148, 6), (7, 50, 5)]
+# (T, B, A): the per-SM kernel, the cluster kernel, the item kernel and the
+# 32-column-tile kernels (here: more steps than a cluster holds); each publishes
+# from the CTA that finishes the loss reduction
+FUSED_SHAPES = [(32, 64 * 148, 6), (7, 50, 5), (9, 8, 4), (300, 40, 5)]
 
 
 def _fused_call(_lib, lib, T, B, A, seed, device):
@@ -87,8 +89,13 @@ def _fused_call(_lib, lib, T, B, A, seed, device):
   return p, keep, nbytes
 
 
-def test_fused_pass_publishes_its_losses_world_of_one():
+@pytest.mark.parametrize('two_launches', [False, True])
+def test_fused_pass_publishes_its_losses_world_of_one(monkeypatch, two_launches):
+  """two_launches: the final reduction left to K3 (as under stream capture),
+  so the library appends the publish / collect launches itself."""
   assert torch.cuda.is_available()
+  if two_launches:
+    monkeypatch.setenv('VTR_NO_INKERNEL_FINISH', '1')
   from scalable_agent_b200 import _lib
   lib = _lib.load()
   device = torch.device('cuda', 0)
@@ -110,7 +117,7 @@ def test_fused_pass_publishes_its_losses_world_of_one():
     text = ctypes.create_string_buffer(512)
     assert lib.vtr_fused_describe(ctypes.byref(p), 1, ctypes.byref(count), text, 512) == 0
     inside = b'peer publish' in text.value
-    assert inside == (B >= 64 * 148), text.value
+    assert inside == (not two_launches or B >= 64 * 148), text.value
     assert inside or b'exchange_publish_kernel' in text.value
     rc = lib.vtr_from_logits_fused_f32(ctypes.byref(p), keep['ws'].data_ptr(), nbytes, stream)
     assert rc == 0, _lib.last_error()
@@ -131,6 +138,38 @@ def test_fused_pass_publishes_its_losses_world_of_one():
     assert rc == 0, _lib.last_error()
     torch.cuda.synchronize()
     assert torch.equal(sums, plain), (sums, plain)
+    # lag 1: the pass hands out the previous step's sums and publishes its own
+    seq += 1
+    p.exchange_seq, p.exchange_lag = seq, 1
+    sums.fill_(-1.0)
+    rc = lib.vtr_from_logits_fused_f32(ctypes.byref(p), keep['ws'].data_ptr(), nbytes, stream)
+    assert rc == 0, _lib.last_error()
+    rc = lib.vtr_exchange_collect_f32(buf.data_ptr(), 4, 1, seq, got.data_ptr(), stream)
+    assert rc == 0, _lib.last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(sums, plain) and torch.equal(got, plain), (sums, got, plain)
+    p.exchange_lag = 0
+
+
+def test_fused_pass_lagged_sums_first_step_writes_nothing():
+  assert torch.cuda.is_available()
+  from scalable_agent_b200 import _lib
+  lib = _lib.load()
+  device = torch.device('cuda', 0)
+  stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+  buf = torch.zeros(lib.vtr_exchange_buffer_bytes(1) // 4, device=device)
+  peers = (ctypes.c_void_p * 1)(buf.data_ptr())
+  p, keep, nbytes = _fused_call(_lib, lib, 7, 50, 5, seed=3, device=device)
+  sums = torch.full((4,), -7.0, device=device)
+  p.exchange_peer_buffers = ctypes.cast(peers, ctypes.POINTER(ctypes.c_void_p))
+  p.exchange_rank, p.exchange_world, p.exchange_seq, p.exchange_lag = 0, 1, 1, 1
+  p.exchange_sums = sums.data_ptr()
+  rc = lib.vtr_from_logits_fused_f32(ctypes.byref(p), keep['ws'].data_ptr(), nbytes, stream)
+  assert rc == 0, _lib.last_error()
+  torch.cuda.synchronize()
+  assert torch.equal(sums, torch.full((4,), -7.0, device=device))
+  p.exchange_lag = 2
+  assert lib.vtr_from_logits_fused_f32(ctypes.byref(p), keep['ws'].data_ptr(), nbytes, stream) == -1
 
 
 def test_fused_pass_rejects_bad_exchange_fields():
@@ -172,6 +211,22 @@ def _fused_worker(rank, world, port, out_dir):
       assert rc == 0, _lib.last_error()
       sums.append((ex.collect() if inside is None else inside).cpu())
       locals_.append(keep['losses'].cpu())
+    # lagged: step k hands out the sums of step k-1; rank 1 is held back now
+    # and then so that the ranks drift
+    lagged = []
+    prev = torch.zeros(4, device=device)
+    for step, (T, B, A) in enumerate(FUSED_SHAPES * 3):
+      p, keep, nbytes = _fused_call(_lib, lib, T, B, A, seed=7000 + 100 * rank + step, device=device)
+      if rank == 1 and step % 4 == 1:
+        torch.cuda._sleep(3000000)
+      ex.attach(p, prev, lag=1)
+      rc = lib.vtr_from_logits_fused_f32(ctypes.byref(p), keep['ws'].data_ptr(), nbytes, stream)
+      assert rc == 0, _lib.last_error()
+      if step > 0:
+        lagged.append(prev.cpu())     # sums of step - 1
+      locals_.append(keep['losses'].cpu())
+    lagged.append(ex.collect().cpu())  # the last step's
+    sums.extend(lagged)
     torch.save((torch.stack(sums), torch.stack(locals_)),
                os.path.join(out_dir, 'f%d.pt' % rank))
   finally:

@@ -50,6 +50,8 @@ def test_random_configuration_matches_oracle(seed):
     paths.append('sm_tile')
   if T <= 256 and A in SPECIAL_A and B <= 16384:
     paths.append('item')
+  if T <= 100 and B <= 16384 and A <= 40:   # chunks of <= 13 steps, a portable cluster
+    paths.append('chunk')
   path = paths[int(rng.integers(0, len(paths)))]
   crho = [None, 1.0, 3.7, 0.5][int(rng.integers(0, 4))]
   cpg = [None, 1.0, 2.2][int(rng.integers(0, 3))]

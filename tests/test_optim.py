@@ -207,7 +207,7 @@ def _sharded_world_of_one(lib, n, steps, momentum):
     rc = lib.vtr_rmsprop_allreduce_f32(
         peers[0], peers[1], peers[2], d_ms.data_ptr(),
         d_mom.data_ptr() if d_mom is not None else None, n, 0, 1, seq,
-        0.01, DECAY, momentum, EPSILON, stream)
+        0.01, DECAY, momentum, EPSILON, None, stream)
     assert rc == 0
     o_var, o_ms, o_mom = oracle.rmsprop_step(o_var, o_ms, o_mom, g, 0.01, DECAY, momentum, EPSILON)
   torch.cuda.synchronize()
@@ -269,6 +269,65 @@ def _worker(rank, world, port, out_dir):
                os.path.join(out_dir, 'o%d.pt' % rank))
   finally:
     dist.destroy_process_group()
+
+
+def _late_worker(rank, world, port, out_dir):
+  """Rank 1 reaches its second optimiser step long after the peer time-out."""
+  import torch.distributed as dist
+  os.environ['MASTER_ADDR'] = '127.0.0.1'
+  os.environ['MASTER_PORT'] = str(port)
+  torch.cuda.set_device(rank)
+  device = torch.device('cuda', rank)
+  dist.init_process_group('nccl', rank=rank, world_size=world, device_id=device)
+  try:
+    from scalable_agent_b200 import _lib, optim
+    lib = _lib.load()
+    assert lib.vtr_get_peer_timeout_ms() == 20000          # the default
+    lib.vtr_set_peer_timeout_ms(50)
+    params = [torch.nn.Parameter(torch.zeros(4096, device=device))]
+    opt = optim.RMSPropOptimizer(params, 0.02, DECAY, 0.0, EPSILON, group=dist.group.WORLD)
+    params[0].grad.fill_(1.0 + rank)
+    opt.step()                                             # step 1: everybody on time
+    torch.cuda.synchronize()
+    opt.check_peers()
+    after_one = params[0].detach().cpu().clone()
+    dist.barrier()
+    if rank == 1:
+      torch.cuda._sleep(int(0.4 * 1.9e9))                  # ~0.4 s on the GPU, 8x the time-out
+    opt.step()                                             # step 2: rank 0 gives up waiting
+    torch.cuda.synchronize()
+    flagged = int(opt.sync[33].item())
+    host_word = int(opt._host_status[0])
+    raised = False
+    try:
+      opt.step()                                           # refuses: the host word is set
+    except RuntimeError as e:
+      raised = 'given up' in str(e)
+    torch.save({'after_one': after_one, 'final': params[0].detach().cpu(),
+                'flagged': flagged, 'host_word': host_word, 'raised': raised},
+               os.path.join(out_dir, 'late%d.pt' % rank))
+  finally:
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sharded_optimizer_flags_a_late_peer_on_every_rank(tmp_path):
+  """A rank that arrives after the time-out must not leave a silently
+  half-updated model: both ranks flag the step (device word, pinned host
+  word, exception on the next step), and neither slice is half-written."""
+  if torch.cuda.device_count() < 2:
+    pytest.skip('needs 2 GPUs')
+  import torch.multiprocessing as mp
+  world = 2
+  mp.spawn(_late_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+  r = [torch.load(tmp_path / ('late%d.pt' % k)) for k in range(world)]
+  assert torch.equal(r[0]['after_one'], r[1]['after_one'])
+  for k in range(world):
+    assert r[k]['flagged'] == 1 and r[k]['host_word'] == 2 and r[k]['raised'], (k, r[k])
+    # each rank's slice is either untouched or fully updated
+    for lo, hi in ((0, 2048), (2048, 4096)):
+      moved = (r[k]['final'][lo:hi] != r[k]['after_one'][lo:hi])
+      assert bool(moved.all()) or not bool(moved.any()), (k, lo)
 
 
 @pytest.mark.gpu

@@ -254,6 +254,61 @@ def test_item_kernel_matches_oracle(api, T, B, A):
   _check_fused(experiment, inp, path='item')
 
 
+@pytest.mark.parametrize('T,B,A', [
+    (5, 2, 3),          # config 1: one chunk, two lanes
+    (100, 32, 9),       # config 2: one cluster of 8 chunks
+    (100, 2048, 9),     # config 3
+    (20, 16384, 18),    # config 4: two chunks
+    (100, 4096, 18),    # the mid point of the sweep
+    (1, 1, 1), (2, 33, 2), (13, 31, 4), (14, 64, 6), (25, 65, 5), (40, 37, 7),
+    (97, 100, 32), (100, 70, 18), (104, 130, 9), (12, 34, 100), (3, 3, 256),
+    (64, 1000, 18), (50, 4100, 3),
+])
+def test_chunk_kernel_matches_oracle(api, T, B, A):
+  """K5 explicitly: T split over a thread-block cluster, chunk aggregates of
+  the affine recurrence composed in a fixed order.  Covers one chunk, the
+  portable cluster sizes, ragged last chunks and column groups, run-time A
+  (rows left in shared memory) and rows that bulk copies cannot take."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T * 1000 + B + A)
+  _check_fused(experiment, inp, path='chunk')
+
+
+def test_chunk_kernel_long_unroll_and_limits(api):
+  """More steps than 8 chunks hold need a cluster above the portable size:
+  either the device schedules it and the result is right, or the call says
+  so; the automatic choice never fails."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(200, 64, 9, seed=200)
+  try:
+    _check_fused(experiment, inp, path='chunk')
+  except ValueError as e:
+    assert 'chunk kernel' in str(e)
+  _check_fused(experiment, inp, path='auto')
+  with pytest.raises(ValueError, match='chunk kernel'):
+    _run_fused(experiment, oracle.synthetic_inputs(300, 4, 9, seed=1), path='chunk')
+
+
+def test_chunk_kernel_options(api, monkeypatch):
+  """Thresholds, reward clipping and done flags on K5; chunk lengths other
+  than the default; and the two-launch form (K3 instead of the last CTA)."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(24, 200, 9, seed=61, reward_clipping=None)
+  inp['rewards'] = inp['raw_rewards']
+  _check_fused(experiment, inp, crho=1.0, cpg=1.0, reward_clipping='soft_asymmetric',
+               done_np=inp['done'], discounting=0.97, path='chunk',
+               ec=0.0033391318945337044)
+  _check_fused(experiment, inp, crho=None, cpg=None, reward_clipping='abs_one',
+               path='chunk', tol=5e-5)
+  for steps in ('3', '8', '13'):
+    monkeypatch.setenv('VTR_CHUNK_STEPS', steps)
+    _check_fused(experiment, inp, reward_clipping='abs_one', path='chunk')
+  monkeypatch.delenv('VTR_CHUNK_STEPS')
+  monkeypatch.setenv('VTR_NO_INKERNEL_FINISH', '1')
+  _check_fused(experiment, inp, reward_clipping='abs_one', path='chunk')
+  _check_fused(experiment, inp, reward_clipping='abs_one', path='item')
+
+
 def test_item_kernel_limits(api):
   _, experiment = api
   with pytest.raises(ValueError, match='item kernel'):
@@ -263,21 +318,31 @@ def test_item_kernel_limits(api):
 
 
 def test_kernels_agree_bitwise(api):
-  """Whatever kernel the heuristics pick, a column gets the same bits."""
+  """The kernels that walk a column step by step (K1a/K1b, K1c) give a column
+  the same bits.  K2 and K5 re-associate the recurrence (a scan; chunk
+  aggregates), so their vs / pg_advantages / gradients agree to rounding, and
+  everything computed before the recurrence is still bit-identical."""
   _, experiment = api
   inp = oracle.synthetic_inputs(60, 2048, 18, seed=77)
   outs = {}
-  for path in ('column', 'sm_tile', 'item'):
+  for path in ('column', 'sm_tile', 'item', 'chunk'):
     args, out = _run_fused(experiment, inp, path=path)
     out.total_loss.backward()
     outs[path] = (out, args['target_policy_logits'].grad, args['values'].grad)
   a = outs['column']
-  for other in ('sm_tile', 'item'):
+  b = outs['sm_tile']
+  for f in a[0].vtrace_returns._fields:
+    assert torch.equal(getattr(a[0].vtrace_returns, f), getattr(b[0].vtrace_returns, f)), f
+  assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+  for other in ('item', 'chunk'):
     b = outs[other]
-    for f in a[0].vtrace_returns._fields:
-      assert torch.equal(getattr(a[0].vtrace_returns, f),
-                         getattr(b[0].vtrace_returns, f)), (other, f)
-    assert torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]), other
+    for f in ('log_rhos', 'behaviour_action_log_probs', 'target_action_log_probs'):
+      assert torch.equal(getattr(a[0].vtrace_returns, f), getattr(b[0].vtrace_returns, f)), (other, f)
+    for f in ('vs', 'pg_advantages'):
+      assert_close(_np(getattr(b[0].vtrace_returns, f)), _np(getattr(a[0].vtrace_returns, f)),
+                   2e-6, '%s %s' % (other, f))
+    assert_close(_np(b[1]), _np(a[1]), 2e-6, other + ' d_logits')
+    assert_close(_np(b[2]), _np(a[2]), 2e-6, other + ' d_values')
 
 
 def test_sm_tile_refuses_unaligned_batch(api):
@@ -339,18 +404,20 @@ def test_target_shape_full_size(api):
   lo, hi = 4096, 4096 + 640
   sl = {k: (inp[k][:, lo:hi] if inp[k].ndim >= 2 else inp[k][lo:hi]).copy()
         for k in FUSED_KEYS}
-  _, out_sl = _run_fused(experiment, sl)
+  _, out_sl = _run_fused(experiment, sl, path='column')
   assert torch.equal(out_sl.vtrace_returns.vs, out.vtrace_returns.vs[:, lo:hi])
   assert torch.equal(out_sl.vtrace_returns.pg_advantages,
                      out.vtrace_returns.pg_advantages[:, lo:hi])
 
 
-def test_bitwise_determinism(api):
+@pytest.mark.parametrize('path,B', [('auto', 1000), ('chunk', 1000), ('item', 96),
+                                    ('column', 1000), ('sm_tile', 1000)])
+def test_bitwise_determinism(api, path, B):
   _, experiment = api
-  inp = oracle.synthetic_inputs(100, 1000, 18, seed=5)
+  inp = oracle.synthetic_inputs(100, B, 18, seed=5)
   results = []
   for _ in range(3):
-    args, out = _run_fused(experiment, inp)
+    args, out = _run_fused(experiment, inp, path=path)
     out.total_loss.backward()
     results.append((out, args['target_policy_logits'].grad.clone(),
                     args['values'].grad.clone()))
