@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define VTR_VERSION 100 /* major*10000 + minor*100 + patch */
+#define VTR_VERSION 200 /* major*10000 + minor*100 + patch */
 
 #define VTR_OK 0
 #define VTR_ERR_INVALID_ARGUMENT (-1) /* NULL required pointer, T/B/A <= 0 ... */
@@ -152,6 +152,12 @@ typedef struct vtr_fused_params {
      2 s, and write their rank-ordered sum here), so a step needs no exchange
      call at all. */
   float* exchange_sums;
+
+  /* float[1] or NULL: the weighted total (= losses[3]) once more, in a buffer
+     of its own - for a caller whose framework wants the differentiable total
+     and the constant component losses in separate tensors (an autograd
+     output may not alias a non-differentiable one).  Needs `losses`. */
+  float* total_loss;
 } vtr_fused_params;
 
 /* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): an

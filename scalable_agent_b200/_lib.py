@@ -56,6 +56,7 @@ class FusedParams(ctypes.Structure):
       ('exchange_seq', ctypes.c_uint32),
       ('exchange_lag', ctypes.c_uint32),
       ('exchange_sums', ctypes.c_void_p),
+      ('total_loss', ctypes.c_void_p),
   ]
 
 

@@ -115,7 +115,11 @@ def from_logits_fused(
     want_grads: bool, path: int, pad_grads: bool = False
 ) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor,
            torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
-  """Returns (vs, pg_adv, log_rhos, b_lp, t_lp, losses[4], d_logits, d_values).
+  """Returns (vs, pg_adv, log_rhos, b_lp, t_lp, losses[5], d_logits, d_values);
+  losses = [pg, baseline, entropy, total, total]: the last element is the
+  weighted total once more, written by the kernel into a slot of its own
+  (vtr_fused_params.total_loss) so that a caller can hand out a
+  differentiable total that does not alias the constant components.
 
   Outputs that were not asked for come back as empty tensors.  With
   `pad_grads` the two gradient tensors get one extra, zeroed time step at the
@@ -133,7 +137,7 @@ def from_logits_fused(
   log_rhos = torch.empty((T, B), **f32) if want_aux else empty()
   b_lp = torch.empty((T, B), **f32) if want_aux else empty()
   t_lp = torch.empty((T, B), **f32) if want_aux else empty()
-  losses = torch.empty(4, **f32) if want_losses else empty()
+  losses = torch.empty(5, **f32) if want_losses else empty()
   Tg = T + 1 if pad_grads else T
   d_logits = torch.empty((Tg, B, A), **f32) if want_grads else empty()
   d_values = torch.empty((Tg, B), **f32) if want_grads else empty()
@@ -171,6 +175,7 @@ def from_logits_fused(
   workspace, ws_bytes = None, 0
   if want_losses:
     p.losses = losses.data_ptr()
+    p.total_loss = losses.data_ptr() + 16
     ws_bytes = lib.vtr_fused_workspace_bytes(T, B, A)
     workspace = torch.empty(ws_bytes // 8, dtype=torch.float64, device=dev)
   with _on(dev):
@@ -191,7 +196,7 @@ def _(behaviour_policy_logits, target_policy_logits, actions, discounts,
   tb = lambda on: new((T, B)) if on else new((0,))
   Tg = T + 1 if pad_grads else T
   return (new((T, B)), new((T, B)), tb(want_aux), tb(want_aux), tb(want_aux),
-          new((4,)) if want_losses else new((0,)),
+          new((5,)) if want_losses else new((0,)),
           new((Tg, B, A)) if want_grads else new((0,)),
           new((Tg, B)) if want_grads else new((0,)))
 
@@ -469,6 +474,9 @@ class FromLogits(torch.autograd.Function):
         clip_pg_rho_threshold, 0.0, 0.0, 0.0, 0, True, False, False, path)
     ctx.save_for_backward(behaviour_policy_logits, target_policy_logits, actions)
     ctx.mark_non_differentiable(vs, pg)
+    # outputs nobody differentiated through come to backward() as None, not
+    # as freshly zero-filled [T, B] tensors
+    ctx.set_materialize_grads(False)
     return vs, pg, log_rhos, b_lp, t_lp
 
   @staticmethod
@@ -476,13 +484,23 @@ class FromLogits(torch.autograd.Function):
   def backward(ctx, g_vs, g_pg, g_log_rhos, g_b_lp, g_t_lp):
     behaviour, target, actions = ctx.saved_tensors
     one = torch.ones(1, dtype=torch.float32, device=target.device)
+
+    def combine(a, sa, b, sb):
+      """sa*a + sb*b over gradients that may be None (= zero)."""
+      parts = [s * g if s != 1 else g for g, s in ((a, sa), (b, sb)) if g is not None]
+      if not parts:
+        return None
+      return (parts[0] if len(parts) == 1 else parts[0] + parts[1]).contiguous()
+
     d_behaviour = d_target = None
     if ctx.needs_input_grad[0]:
-      d_behaviour = call(pg_loss_bwd, behaviour, actions,
-                                (g_log_rhos - g_b_lp).contiguous(), one)
+      w = combine(g_log_rhos, 1, g_b_lp, -1)
+      if w is not None:
+        d_behaviour = call(pg_loss_bwd, behaviour, actions, w, one)
     if ctx.needs_input_grad[1]:
-      d_target = call(pg_loss_bwd, target, actions,
-                             (-(g_log_rhos + g_t_lp)).contiguous(), one)
+      w = combine(g_log_rhos, -1, g_t_lp, -1)
+      if w is not None:
+        d_target = call(pg_loss_bwd, target, actions, w, one)
     return (d_behaviour, d_target) + (None,) * 8
 
 
@@ -507,8 +525,9 @@ class FusedLoss(torch.autograd.Function):
         clip_pg_rho_threshold, baseline_cost, entropy_cost, discounting,
         reward_clip_mode, want_aux, True, want_grads, path)
     ctx.save_for_backward(d_logits, d_values)
-    total = losses[3].clone()
+    total = losses[4].clone()
     ctx.backward_ran = False
+    ctx.set_materialize_grads(False)
     ctx.mark_non_differentiable(vs, pg, log_rhos, b_lp, t_lp, losses)
     return total, losses, vs, pg, log_rhos, b_lp, t_lp
 
@@ -520,9 +539,12 @@ class FusedLoss(torch.autograd.Function):
                          'backward can run only once per forward')
     ctx.backward_ran = True
     d_logits, d_values = ctx.saved_tensors
-    g = _scalar_f32(g_total)
-    call(scale_inplace, d_logits, g)
-    call(scale_inplace, d_values, g)
+    if g_total is None:
+      return (None,) * 16
+    if d_logits.numel():       # empty: no differentiated input asked for a gradient
+      g = _scalar_f32(g_total)
+      call(scale_inplace, d_logits, g)
+      call(scale_inplace, d_values, g)
     grads = [None] * 16
     if ctx.needs_input_grad[1]:
       grads[1] = d_logits
@@ -556,7 +578,8 @@ class FusedLearnerLoss(torch.autograd.Function):
         discounting, reward_clip_mode, want_aux, True, want_grads, path, True)
     ctx.save_for_backward(d_logits, d_values)
     ctx.backward_ran = False
-    total = losses[3].clone()
+    total = losses[4].clone()
+    ctx.set_materialize_grads(False)
     ctx.mark_non_differentiable(vs, pg, log_rhos, b_lp, t_lp, losses)
     return total, losses, vs, pg, log_rhos, b_lp, t_lp
 
@@ -568,9 +591,12 @@ class FusedLearnerLoss(torch.autograd.Function):
                          'place; backward can run only once per forward')
     ctx.backward_ran = True
     d_logits, d_values = ctx.saved_tensors
-    g = _scalar_f32(g_total)
-    call(scale_inplace, d_logits, g)
-    call(scale_inplace, d_values, g)
+    if g_total is None:
+      return (None,) * 14
+    if d_logits.numel():
+      g = _scalar_f32(g_total)
+      call(scale_inplace, d_logits, g)
+      call(scale_inplace, d_values, g)
     grads = [None] * 14
     if ctx.needs_input_grad[0]:
       grads[0] = d_logits

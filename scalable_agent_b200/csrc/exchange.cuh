@@ -21,13 +21,13 @@ struct PeerBuffers {
 };
 
 // Stores values[0..n) and then the sequence number into slot [seq % 4][rank]
-// of ONE peer's buffer: values first, a system-wide fence, then the flag with
-// release semantics, so a peer that sees the flag sees the values.
+// of ONE peer's buffer: values first, then the flag with system-scope release
+// semantics (which orders this thread's earlier stores before it), so a peer
+// that sees the flag sees the values.
 __device__ __forceinline__ void exchange_publish_to_peer(float* peer, const float* values, int n,
                                                          int rank, int world, uint32_t seq) {
   float* slot = peer + (static_cast<size_t>(seq % kExchangeSlots) * world + rank) * kSlotFloats;
   for (int i = 0; i < n; ++i) slot[i] = values[i];
-  __threadfence_system();
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(slot + 7)),
                "r"(seq)
                : "memory");
@@ -38,7 +38,6 @@ __device__ __forceinline__ void exchange_publish4_to_peer(float* peer, float v0,
                                                           float v3, int rank, int world, uint32_t seq) {
   float* slot = peer + (static_cast<size_t>(seq % kExchangeSlots) * world + rank) * kSlotFloats;
   *reinterpret_cast<float4*>(slot) = make_float4(v0, v1, v2, v3);  // slots are 32-byte aligned
-  __threadfence_system();
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(slot + 7)),
                "r"(seq)
                : "memory");

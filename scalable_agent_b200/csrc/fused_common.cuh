@@ -38,6 +38,7 @@ struct FusedArgs {
   double* partials;  // loss partials, or null
   float* losses;       // K1c only: final losses written by the last tile to finish
   double* losses_f64;  // K1c only
+  float* total_out;    // the weighted total once more, or null (vtr_fused_params.total_loss)
 };
 
 constexpr int kColumnsPerTile = 32;

@@ -81,6 +81,7 @@ __device__ __forceinline__ void finish_losses(const FusedArgs& a, const FinishAr
     }
     if (fin.losses_f64)
       fin.losses_f64[0] = pg, fin.losses_f64[1] = bl, fin.losses_f64[2] = ent, fin.losses_f64[3] = total;
+    if (a.total_out) *a.total_out = static_cast<float>(total);
   }
 }
 

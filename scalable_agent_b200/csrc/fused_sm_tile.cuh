@@ -52,9 +52,10 @@ struct SmTileArgs {
   int staging_bufs;  // 1 or 2 gradient staging rows per consumer warp
   int num_sm;        // SMs of the device
   int waves;         // tiles per SM (grid = num_sm * waves) when balancing
-  unsigned int* cursor;  // workspace header (zeroed): [0] column cursor and [1] tiles served
+  unsigned int* cursor;  // 256 counters, zero on entry: [0] column cursor and [1] tiles served
                          // (one 64-bit counter), [2] finished groups, [16 + k] granules
                          // of group k written so far; or null
+  int self_clean;        // the tile that finishes the reduction zeroes the counters again
   double* group_partials;  // [groups][3], second level of the loss reduction
   int group_gran;          // granules (of 4 columns) per reduction group
   float smoothing;         // least weight of the newest measurement in the speed table
@@ -475,6 +476,20 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
               }
               if (a.losses_f64)
                 a.losses_f64[0] = pg, a.losses_f64[1] = bl, a.losses_f64[2] = ent, a.losses_f64[3] = total;
+              if (a.total_out) *a.total_out = static_cast<float>(total);
+            }
+            if (args.self_clean) {
+              // Counters that belong to the library go back to zero for the
+              // next launch that is handed them.  Every group is complete, so
+              // the only accesses still to come are the cursor draws of tiles
+              // that have not started yet (they will find no columns left):
+              // wait until all gridDim.x tiles have drawn.
+              if (lane == 0) {
+                const volatile unsigned int* served = args.cursor + 1;
+                while (*served < gridDim.x) __nanosleep(200);
+              }
+              __syncwarp();
+              for (int i = lane; i < 256; i += 32) args.cursor[i] = 0u;
             }
           }
         }

@@ -49,7 +49,8 @@ __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __rest
                                                             int n, float baseline_cost,
                                                             float entropy_cost,
                                                             float* __restrict__ losses,
-                                                            double* __restrict__ losses_f64) {
+                                                            double* __restrict__ losses_f64,
+                                                            float* __restrict__ total_out) {
   __shared__ double sh[3][256];
   const int tid = threadIdx.x;
   double s0 = 0.0, s1 = 0.0, s2 = 0.0;
@@ -75,6 +76,7 @@ __global__ void __launch_bounds__(256) reduce_losses_kernel(const double* __rest
       losses[2] = static_cast<float>(ent), losses[3] = static_cast<float>(total);
     }
     if (losses_f64) losses_f64[0] = pg, losses_f64[1] = bl, losses_f64[2] = ent, losses_f64[3] = total;
+    if (total_out) *total_out = static_cast<float>(total);
   }
 }
 
@@ -164,6 +166,7 @@ static void fill_args(FusedArgs& a, const vtr_fused_params* p, double* partials)
   a.d_logits = p->d_target_logits, a.d_values = p->d_values;
   a.partials = partials;
   a.losses = nullptr, a.losses_f64 = nullptr;
+  a.total_out = p->total_loss;
   a.depth = 0, a.slot_floats = 0, a.tma_in_ok = 0, a.tma_out_ok = 0;
 }
 
@@ -217,6 +220,57 @@ static int dispatch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaS
   }
 }
 
+// ---------------------------------------------------------------------------
+// Tickets for the in-kernel final reduction (fused_finish.cuh).  The "who
+// finished last" counter must be zero when a launch starts.  Zeroing it in the
+// caller's workspace would cost a second stream operation per call - as much
+// as the kernel itself on the small shapes - so the counters live in a ring
+// inside the library: zero at load, each launch takes the next one, and the
+// CTA that finishes last puts it back to zero.  A counter is handed out again
+// kTicketRing launches later; a GPU runs at most 128 kernels at a time, so two
+// launches never hold the same counter.  A launch that is being captured into
+// a graph will be replayed with the counter it was captured with, any number
+// of times and at any later moment, so it gets one of kTicketCaptured counters
+// that are never handed out again; once those are used up captured launches
+// leave the stage to K3.
+// ---------------------------------------------------------------------------
+constexpr int kTicketRing = 256;
+constexpr int kTicketCaptured = 256;
+constexpr int kTicketWords = 256;  // counters of one launch: K1c uses all, the others one
+static __device__ unsigned int g_finish_tickets[(kTicketRing + kTicketCaptured) * kTicketWords];
+
+// *out: kTicketWords zeroed counters for one launch, or null (then the caller
+// zeroes counters of its own, or leaves the last stage to K3).
+static int next_ticket(cudaStream_t stream, unsigned int** out) {
+  constexpr int kMaxDevices = 64;
+  static unsigned int* base[kMaxDevices] = {};
+  static std::mutex mu;
+  static std::atomic<unsigned int> turn{0}, captured{0};
+  *out = nullptr;
+  cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+  VTR_CUDA_CHECK(cudaStreamIsCapturing(stream, &capturing));
+  int dev = 0;
+  VTR_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(VTR_ERR_UNSUPPORTED, "device index %d", dev);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!base[dev]) {
+      if (capturing != cudaStreamCaptureStatusNone) return VTR_OK;  // no symbol lookup while capturing
+      void* ptr = nullptr;
+      VTR_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_finish_tickets));
+      base[dev] = static_cast<unsigned int*>(ptr);
+    }
+  }
+  if (capturing != cudaStreamCaptureStatusNone) {
+    const unsigned int k = captured.fetch_add(1u, std::memory_order_relaxed);
+    if (k < static_cast<unsigned int>(kTicketCaptured))
+      *out = base[dev] + static_cast<size_t>(kTicketRing + k) * kTicketWords;
+    return VTR_OK;
+  }
+  *out = base[dev] + static_cast<size_t>(turn.fetch_add(1u, std::memory_order_relaxed) % kTicketRing) * kTicketWords;
+  return VTR_OK;
+}
+
 // Workspace layout (vtr_fused_workspace_bytes): an 8 KB header -- K1c's column
 // cursor, its finished-group ticket and per-group granule counters in the
 // first KB (zeroed by the library before every K1c launch), its group
@@ -265,7 +319,18 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   args.groups = (cap_cols + 31) / 32;
   args.num_sm = sm;
   args.waves = waves;
-  args.cursor = balance ? static_cast<unsigned int*>(header) : nullptr;
+  // The counters: from the library's ring, which needs no zeroing (the tile
+  // that finishes the reduction leaves them zero), else the first KB of the
+  // workspace, zeroed with a memset before the launch.
+  args.cursor = nullptr, args.self_clean = 0;
+  if (balance) {
+    unsigned int* ring = nullptr;
+    const bool in_kernel_finish = p->losses || p->losses_f64;
+    if (in_kernel_finish && !g_plan.dry_run && !getenv("VTR_SM_MEMSET"))
+      if (int rc = next_ticket(stream, &ring)) return rc;
+    args.cursor = ring ? ring : static_cast<unsigned int*>(header);
+    args.self_clean = ring != nullptr;
+  }
   args.group_partials = balance ? reinterpret_cast<double*>(static_cast<char*>(header) +
                                                             kWorkspaceCounterBytes)
                                 : nullptr;
@@ -327,58 +392,11 @@ static int run_sm_tile_path(const vtr_fused_params* p, void* header, double* par
   if (depth < 1) depth = 1;
   args.f.depth = static_cast<int>(depth);
   const size_t smem = fixed + depth * slot_bytes;
-  if (balance && !g_plan.dry_run)
+  if (balance && !args.self_clean && !g_plan.dry_run)
     VTR_CUDA_CHECK(cudaMemsetAsync(header, 0, kWorkspaceCounterBytes, stream));
   *num_partials = total_gran;
   return grads ? dispatch_sm_tile<true>(args, grid, smem, stream)
                : dispatch_sm_tile<false>(args, grid, smem, stream);
-}
-
-// ---------------------------------------------------------------------------
-// Tickets for the in-kernel final reduction (fused_finish.cuh).  The "who
-// finished last" counter must be zero when a launch starts.  Zeroing it in the
-// caller's workspace would cost a second stream operation per call - as much
-// as the kernel itself on the small shapes - so the counters live in a ring
-// inside the library: zero at load, each launch takes the next one, and the
-// CTA that finishes last puts it back to zero.  A counter is handed out again
-// kTicketRing launches later; a GPU runs at most 128 kernels at a time, so two
-// launches never hold the same counter.  A launch that is being captured into
-// a graph will be replayed with the counter it was captured with, any number
-// of times and at any later moment, so it gets one of kTicketCaptured counters
-// that are never handed out again; once those are used up captured launches
-// leave the stage to K3.
-// ---------------------------------------------------------------------------
-constexpr int kTicketRing = 1024;
-constexpr int kTicketCaptured = 1024;
-static __device__ unsigned int g_finish_tickets[kTicketRing + kTicketCaptured];
-
-static int next_ticket(cudaStream_t stream, unsigned int** out) {
-  constexpr int kMaxDevices = 64;
-  static unsigned int* base[kMaxDevices] = {};
-  static std::mutex mu;
-  static std::atomic<unsigned int> turn{0}, captured{0};
-  *out = nullptr;
-  cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
-  VTR_CUDA_CHECK(cudaStreamIsCapturing(stream, &capturing));
-  int dev = 0;
-  VTR_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= kMaxDevices) return fail(VTR_ERR_UNSUPPORTED, "device index %d", dev);
-  {
-    std::lock_guard<std::mutex> lock(mu);
-    if (!base[dev]) {
-      if (capturing != cudaStreamCaptureStatusNone) return VTR_OK;  // no symbol lookup while capturing
-      void* ptr = nullptr;
-      VTR_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_finish_tickets));
-      base[dev] = static_cast<unsigned int*>(ptr);
-    }
-  }
-  if (capturing != cudaStreamCaptureStatusNone) {
-    const unsigned int k = captured.fetch_add(1u, std::memory_order_relaxed);
-    if (k < static_cast<unsigned int>(kTicketCaptured)) *out = base[dev] + kTicketRing + k;
-    return VTR_OK;
-  }
-  *out = base[dev] + turn.fetch_add(1u, std::memory_order_relaxed) % kTicketRing;
-  return VTR_OK;
 }
 
 // Fills the in-kernel final stage of K2/K5.  `wanted`: losses were asked for
@@ -740,9 +758,9 @@ extern "C" size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A) {
   return vtr::kWorkspaceHeaderBytes + partials * 3 * sizeof(double);
 }
 
-extern "C" int vtr_reduce_losses(const double* partials, int32_t num_partials,
-                                 float baseline_cost, float entropy_cost, float* losses,
-                                 double* losses_f64, void* stream) {
+static int reduce_losses(const double* partials, int32_t num_partials, float baseline_cost,
+                         float entropy_cost, float* losses, double* losses_f64, float* total_out,
+                         void* stream) {
   if (!partials || num_partials <= 0) return vtr::fail(VTR_ERR_INVALID_ARGUMENT, "vtr_reduce_losses: no partials");
   if (!losses && !losses_f64) return vtr::fail(VTR_ERR_INVALID_ARGUMENT, "vtr_reduce_losses: no output");
   if (vtr::g_plan.dry_run) {
@@ -750,9 +768,16 @@ extern "C" int vtr_reduce_losses(const double* partials, int32_t num_partials,
     return VTR_OK;
   }
   vtr::reduce_losses_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      partials, num_partials, baseline_cost, entropy_cost, losses, losses_f64);
+      partials, num_partials, baseline_cost, entropy_cost, losses, losses_f64, total_out);
   VTR_CUDA_CHECK(cudaGetLastError());
   return VTR_OK;
+}
+
+extern "C" int vtr_reduce_losses(const double* partials, int32_t num_partials,
+                                 float baseline_cost, float entropy_cost, float* losses,
+                                 double* losses_f64, void* stream) {
+  return reduce_losses(partials, num_partials, baseline_cost, entropy_cost, losses, losses_f64, nullptr,
+                       stream);
 }
 
 extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* workspace,
@@ -782,6 +807,8 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
     if (!vtr::aligned(q, 4)) return fail(VTR_ERR_MISALIGNED, "a float/int32 pointer is not 4-byte aligned");
   if (!vtr::aligned(p->losses_f64, 8)) return fail(VTR_ERR_MISALIGNED, "losses_f64 is not 8-byte aligned");
 
+  if (p->total_loss && !p->losses) return fail(VTR_ERR_INVALID_ARGUMENT, "total_loss needs `losses`");
+  if (!vtr::aligned(p->total_loss, 4)) return fail(VTR_ERR_MISALIGNED, "total_loss is not 4-byte aligned");
   const bool want_exchange = p->exchange_peer_buffers != nullptr;
   if (want_exchange) {
     if (!p->losses) return fail(VTR_ERR_INVALID_ARGUMENT, "exchange_peer_buffers needs `losses`");
@@ -837,8 +864,8 @@ extern "C" int vtr_from_logits_fused_f32(const vtr_fused_params* p, void* worksp
   }
   if (rc) return rc;
   if (want_losses && !losses_done) {
-    rc = vtr_reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
-                           p->losses_f64, stream);
+    rc = reduce_losses(partials, num_partials, p->baseline_cost, p->entropy_cost, p->losses,
+                       p->losses_f64, p->total_loss, stream);
     if (rc) return rc;
   }
   if (want_exchange && !exchange_done) {

@@ -399,7 +399,9 @@ extern "C" int vtr_baseline_loss_bwd_f32(const float* advantages, const float* g
 }
 
 extern "C" int vtr_scale_inplace_f32(float* x, const float* scale, int64_t n, void* stream) {
-  if (!x || !scale || n <= 0) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_scale_inplace: NULL pointer or n <= 0");
+  if (n < 0) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_scale_inplace: n < 0");
+  if (n == 0) return VTR_OK;  // nothing to scale (e.g. a gradient nobody asked for)
+  if (!x || !scale) return fail(VTR_ERR_INVALID_ARGUMENT, "vtr_scale_inplace: NULL pointer");
   vtr::DeviceInfo dev;
   if (int rc = vtr::device_info(&dev)) return rc;
   long blocks = (n + 255) / 256;

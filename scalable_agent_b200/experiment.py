@@ -15,6 +15,7 @@ import collections
 
 import torch
 
+from scalable_agent_b200 import _ext
 from scalable_agent_b200 import _lib
 from scalable_agent_b200 import _ops
 from scalable_agent_b200 import vtrace
@@ -24,6 +25,28 @@ VTraceLossReturns = collections.namedtuple(
     'VTraceLossReturns',
     ['total_loss', 'policy_gradient_loss', 'baseline_loss', 'entropy_loss',
      'vtrace_returns'])
+
+
+def _device_ready(*tensors_and_dtypes):
+  """True if every (tensor, dtype) pair is already what the kernels take: a
+  contiguous CUDA tensor of that dtype.  Then the C++ host layer does the
+  rest (checks included); anything else goes through the coercions of the
+  Python layer first."""
+  for t, dtype in tensors_and_dtypes:
+    if not (type(t) is torch.Tensor or isinstance(t, torch.Tensor)):
+      return False
+    if not t.is_cuda or t.dtype is not dtype or not t.is_contiguous():
+      return False
+  return True
+
+
+def _returns(total, losses, vs, pg, log_rhos, b_lp, t_lp):
+  return VTraceLossReturns(
+      total_loss=total, policy_gradient_loss=losses[0],
+      baseline_loss=losses[1], entropy_loss=losses[2],
+      vtrace_returns=vtrace.VTraceFromLogitsReturns(
+          vs=vs, pg_advantages=pg, log_rhos=log_rhos,
+          behaviour_action_log_probs=b_lp, target_action_log_probs=t_lp))
 
 
 def compute_baseline_loss(advantages):
@@ -92,6 +115,26 @@ def compute_vtrace_loss(
     entropy_loss, vtrace_returns).  Only `total_loss` is differentiable; the
     component losses are reported unweighted, for logging.
   """
+  if reward_clipping not in _lib.REWARD_CLIP_MODES:
+    raise ValueError('unknown reward_clipping %r' % (reward_clipping,))
+  if path not in _lib.PATHS:
+    raise ValueError('unknown path %r' % (path,))
+  ext = None if torch.compiler.is_compiling() else _ext.get()
+  f32 = torch.float32
+  if ext is not None and _device_ready(
+      (behaviour_policy_logits, f32), (target_policy_logits, f32),
+      (actions, torch.int32), (rewards, f32), (values, f32), (bootstrap_value, f32),
+      (done, torch.bool) if done is not None else (discounts, f32)):
+    # The C++ host layer: same checks, same kernels, a fraction of the host time.
+    return _returns(*ext.fused_loss(
+        behaviour_policy_logits, target_policy_logits, actions,
+        None if done is not None else discounts, rewards, values, bootstrap_value,
+        done.view(torch.uint8) if done is not None else None,
+        _threshold(clip_rho_threshold, 'clip_rho_threshold'),
+        _threshold(clip_pg_rho_threshold, 'clip_pg_rho_threshold'),
+        float(baseline_cost), float(entropy_cost), float(discounting),
+        _lib.REWARD_CLIP_MODES[reward_clipping], bool(return_aux), _lib.PATHS[path]))
+
   dev = _device_of(behaviour_policy_logits, target_policy_logits, actions,
                    discounts, rewards, values, bootstrap_value)
   behaviour_policy_logits = _to(behaviour_policy_logits, torch.float32, dev)
@@ -175,6 +218,23 @@ def compute_learner_loss(
 
   Returns a `VTraceLossReturns`; only `total_loss` is differentiable.
   """
+  if reward_clipping not in _lib.REWARD_CLIP_MODES:
+    raise ValueError('unknown reward_clipping %r' % (reward_clipping,))
+  if path not in _lib.PATHS:
+    raise ValueError('unknown path %r' % (path,))
+  ext = None if torch.compiler.is_compiling() else _ext.get()
+  f32 = torch.float32
+  if ext is not None and _device_ready(
+      (learner_policy_logits, f32), (learner_baseline, f32), (behaviour_policy_logits, f32),
+      (actions, torch.int32), (rewards, f32), (done, torch.bool)):
+    return _returns(*ext.fused_learner_loss(
+        learner_policy_logits, learner_baseline, behaviour_policy_logits, actions,
+        rewards, done.view(torch.uint8),
+        _threshold(clip_rho_threshold, 'clip_rho_threshold'),
+        _threshold(clip_pg_rho_threshold, 'clip_pg_rho_threshold'),
+        float(baseline_cost), float(entropy_cost), float(discounting),
+        _lib.REWARD_CLIP_MODES[reward_clipping], bool(return_aux), _lib.PATHS[path]))
+
   dev = _device_of(learner_policy_logits, learner_baseline,
                    behaviour_policy_logits)
   learner_policy_logits = _to(learner_policy_logits, torch.float32, dev)

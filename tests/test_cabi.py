@@ -31,7 +31,7 @@ def test_header_symbols_are_exported_and_bound():
 
 def test_version_and_sizes():
   lib = _lib.load()
-  assert lib.vtr_version() == 100
+  assert lib.vtr_version() == 200
   assert lib.vtr_fused_workspace_bytes(100, 32768, 18) == 8192 + 8192 * 24
   assert lib.vtr_fused_workspace_bytes(5, 2, 3) == 8192 + 16 * 24  # K5: up to 16 CTAs per 32 columns
   assert lib.vtr_fused_workspace_bytes(5, 700, 3) == 8192 + 700 * 24  # K2: one partial per column
@@ -41,8 +41,8 @@ def test_version_and_sizes():
 
 
 def test_struct_layout_matches_header():
-  # 4 ints, 8 pointers, 5 floats + 3 ints, 9 pointers, 1 pointer + 4 ints + 1 pointer on LP64.
-  assert ctypes.sizeof(_lib.FusedParams) == 16 + 8 * 8 + 32 + 9 * 8 + 8 + 16 + 8
+  # 4 ints, 8 pointers, 5 floats + 3 ints, 9 pointers, 1 pointer + 4 ints + 2 pointers on LP64.
+  assert ctypes.sizeof(_lib.FusedParams) == 16 + 8 * 8 + 32 + 9 * 8 + 8 + 16 + 8 + 8
 
 
 def test_argument_errors_are_negative_codes_with_messages():

@@ -8,21 +8,57 @@ tomorrow (a short last tile, a batch one column past a tile, more time steps
 than ring slots, an unaligned row, ...).
 
 Tolerance: 1e-5 scaled, the bound of every other GPU test, whenever both
-importance weights are clipped at 1 (the reference's defaults, vtrace.py:74).
-With a looser or no clip the weights reach 8-14 on these inputs, v_s grows
-with them and float32 itself gives out earlier: the op-for-op float32 port of
-the reference (oracle/cpu_port.py) is 1.1e-5 ... 2.1e-5 away from the float64
-oracle on exactly these configurations, so they are held to 5e-5."""
+importance weights are clipped at 1 or below (the reference's defaults,
+vtrace.py:74).  With a looser or no clip the weights reach 8-14 on these
+inputs, v_s grows with them and float32 itself gives out earlier: the
+op-for-op float32 port of the reference (oracle/cpu_port.py) is 1.1e-5 ...
+2.1e-5 away from the float64 oracle on exactly these configurations.  That is
+asserted, not assumed: for every such case the port is run on the same inputs
+and the kernel is held to max(1e-5, 2 x the port's own error), never more than
+5e-5.  (Both are float32 evaluations of the same expression with different
+rounding sequences - torch's vectorised expf and one pass per op there, ex2 /
+FMA and one fused pass here - so neither is uniformly the closer one; the
+largest kernel / port ratio seen over the 48 cases is 1.50, at 1.7e-5.)"""
 import numpy as np
 import pytest
 import torch
 
+from oracle import cpu_port
 from oracle import vtrace_oracle as oracle
-from tests.test_vtrace_gpu import _check_fused
+from tests.test_vtrace_gpu import FUSED_KEYS, _check_fused
 
 pytestmark = pytest.mark.gpu
 
 SPECIAL_A = (3, 4, 6, 9, 18)
+
+
+def _scaled_err(x, ref):
+  x = np.asarray(x, dtype=np.float64)
+  ref = np.asarray(ref, dtype=np.float64)
+  return float(np.max(np.abs(x - ref) / np.maximum(1.0, np.abs(ref)))) if ref.size else 0.0
+
+
+def _port_error(inp, crho, cpg, bc, ec, clip, done, discounting):
+  """Largest scaled error of the float32 op-for-op port of the reference
+  against the float64 oracle, over every output the kernel is checked on."""
+  rewards = oracle.clip_rewards(inp['rewards'], clip).astype(np.float32)
+  discounts = inp['discounts']
+  if done is not None:
+    discounts = oracle.discounts_from_done(done, discounting).astype(np.float32)
+  args = dict(inp, rewards=rewards, discounts=discounts)
+  ref = oracle.fused_vtrace_loss(*[args[k] for k in FUSED_KEYS], crho, cpg, bc, ec)
+  torch.set_num_threads(max(1, torch.get_num_threads()))
+  losses, d_logits, d_values, vs, pg = cpu_port.learner_loss(
+      *[torch.from_numpy(np.ascontiguousarray(args[k])) for k in FUSED_KEYS],
+      baseline_cost=bc, entropy_cost=ec, clip_rho_threshold=crho,
+      clip_pg_rho_threshold=cpg)
+  total = float(losses[0]) + bc * float(losses[1]) + ec * float(losses[2])
+  return max(
+      _scaled_err(vs.numpy(), ref.vs), _scaled_err(pg.numpy(), ref.pg_advantages),
+      _scaled_err(d_logits.numpy(), ref.d_target_logits),
+      _scaled_err(d_values.numpy(), ref.d_values),
+      _scaled_err(losses.numpy(), [ref.pg_loss, ref.baseline_loss, ref.entropy_loss]),
+      _scaled_err(total, ref.total_loss))
 
 
 def _draw(rng):
@@ -61,13 +97,19 @@ def test_random_configuration_matches_oracle(seed):
   use_done = bool(rng.integers(0, 2))
   inp = oracle.synthetic_inputs(T, B, A, seed=seed, reward_clipping=None)
   inp['rewards'] = inp['raw_rewards']
-  tol = 1e-5 if (crho == 1.0 or crho == 0.5) and cpg == 1.0 else 5e-5
+  discounting = float(rng.choice([0.99, 0.9, 1.0])) if use_done else 0.99
+  tol = 1e-5
+  if not ((crho == 1.0 or crho == 0.5) and cpg == 1.0):
+    port_err = _port_error(inp, crho, cpg, bc, ec, clip,
+                           inp['done'] if use_done else None, discounting)
+    tol = max(1e-5, 2.0 * port_err)
+    assert tol <= 5e-5, 'the float32 port itself is %.2e off on this case' % port_err
   kw = dict(crho=crho, cpg=cpg, bc=bc, ec=ec, path=path, tol=tol)
   if clip is not None:
     kw['reward_clipping'] = clip
   if use_done:
     kw['done_np'] = inp['done']
-    kw['discounting'] = float(rng.choice([0.99, 0.9, 1.0]))
+    kw['discounting'] = discounting
   try:
     _check_fused(experiment, inp, **kw)
   except AssertionError as e:
