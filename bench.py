@@ -287,9 +287,10 @@ def run_gpu(args):
       raise SystemExit('bench.py --scaling strong: B must be a multiple of 4 * ranks')
     B //= world
   K, W = args.steps, args.warmup
-  # The per-SM speed table behind the tile sizes settles within a handful of
-  # calls: a short, unreported pre-pass makes sure of that whatever --warmup is.
-  PRE = max(0, 10 - W)
+  # The per-SM speed table behind the tile sizes is a running mean over an
+  # SM's first 20 tiles: an unreported pre-pass makes sure it has settled
+  # whatever --warmup is (its length is in the line, run.untimed_pre_pass_steps).
+  PRE = max(0, 30 - W)
 
   # Inputs + outputs of one step must not fit the 126 MB L2, or steps would be
   # served from it: small per-GPU batches (strong scaling) rotate over several

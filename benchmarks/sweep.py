@@ -94,6 +94,9 @@ def surface(args, device, peak):
           ('from_importance_weights [T,B]', rows * 24 + 4 * B,
            lambda: vtrace.from_importance_weights(log_rhos, inp['discounts'], inp['rewards'],
                                                   inp['values'], inp['bootstrap_value'])),
+          ('from_importance_weights [T,B], op only', rows * 24 + 4 * B,
+           lambda: _ops.call(_ops.from_importance_weights, log_rhos, inp['discounts'], inp['rewards'],
+                             inp['values'].reshape(T, B, 1), inp['bootstrap_value'], 1, 0, 1.0, 1.0)),
           ('from_importance_weights [T,B,1]x[T,B,42]', rows * (8 + 16 * C) + 4 * B * C,
            lambda: vtrace.from_importance_weights(log_rhos[..., None], inp['discounts'][..., None],
                                                   rew_c, val_c, boot_c)),

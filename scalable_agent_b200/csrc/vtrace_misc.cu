@@ -7,9 +7,12 @@
 //   compute_baseline_loss              experiment.py:324-328  (+ backward)
 // All reductions are two-stage with a fixed order (no atomics).
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.h"
+#include "fused_common.cuh"
 #include "ptx.cuh"
+#include "vtrace_math.cuh"
 
 namespace vtr {
 
@@ -60,6 +63,89 @@ __global__ void __launch_bounds__(128) importance_weights_kernel(const __grid_co
     a.vs[t * cols + j] = vs;
     a.pg[t * cols + j] = pg;
     v_next = val;
+    vs_next = vs;
+  }
+}
+
+// K4 with the unroll split over the threads of a block: for a batch of a few
+// ten thousand columns one thread per column leaves an SM with a couple of
+// hundred threads and as many loads in flight - a third of the memory
+// bandwidth.  Here 32 adjacent columns share a block of kIwChunks x 32
+// threads; thread (c, lane) owns chunk c of its column's time steps.  The
+// recurrence acc_t = gain_t acc_{t+1} + delta_t (vtrace.py:250-262) is affine,
+// so a chunk first walks its steps from acc = 0 and publishes (prod gain, acc)
+// in shared memory, folds the aggregates of the later-time chunks in index
+// order into the value that enters it, and then walks its steps again from
+// that value - inside a chunk the operations are those of the sequential
+// recurrence - writing vs and pg_advantages.  The second walk re-reads what
+// the first one brought into L1/L2.
+constexpr int kIwChunks = 8;
+
+struct IwStep {
+  float gain, delta, rho_pg, rew, disc, val;
+};
+
+__device__ __forceinline__ IwStep iw_load(const IwArgs& a, long cols, long j, long rho_col, long rho_stride,
+                                          long disc_col, long disc_stride, int t, float v_next) {
+  const float log_rho = __ldg(a.log_rhos + t * rho_stride + rho_col);
+  IwStep s;
+  s.disc = __ldg(a.discounts + t * disc_stride + disc_col);
+  s.rew = __ldg(a.rewards + t * cols + j);
+  s.val = __ldg(a.values + t * cols + j);
+  const float rho = expf(log_rho);                                       // :235
+  const float rho_hat = a.no_clip_rho ? rho : fminf(a.clip_rho, rho);    // :236-239
+  const float c = fminf(1.0f, rho);                                      // :241
+  s.rho_pg = a.no_clip_pg ? rho : fminf(a.clip_pg, rho);                 // :270-274
+  s.delta = rho_hat * (s.rew + s.disc * v_next - s.val);                 // :245
+  s.gain = s.disc * c;
+  return s;
+}
+
+__global__ void __launch_bounds__(32 * kIwChunks)
+    importance_weights_chunk_kernel(const __grid_constant__ IwArgs a) {
+  __shared__ float sh_prod[kIwChunks][32], sh_acc[kIwChunks][32];
+  const long cols = static_cast<long>(a.B) * a.C;
+  const int lane = threadIdx.x & 31, c = threadIdx.x >> 5;
+  const long j = static_cast<long>(blockIdx.x) * 32 + lane;
+  const bool live = j < cols;
+  const long jj = live ? j : 0;
+  const long jb = jj / a.C;
+  const long rho_col = a.rho_bcast ? jb : jj, rho_stride = a.rho_bcast ? a.B : cols;
+  const long disc_col = a.disc_bcast ? jb : jj, disc_stride = a.disc_bcast ? a.B : cols;
+  const int S = (a.T + kIwChunks - 1) / kIwChunks;
+  const int it0 = c * S, it1 = min(a.T, it0 + S);  // steps counted from the end: t = T-1-it
+
+  // first walk: the chunk's aggregate
+  float acc = 0.0f, prod = 1.0f;
+  if (live) {
+    float v_next = it0 == 0 ? a.bootstrap[jj] : __ldg(a.values + (a.T - it0) * cols + jj);
+#pragma unroll 4
+    for (int it = it0; it < it1; ++it) {
+      const IwStep s = iw_load(a, cols, jj, rho_col, rho_stride, disc_col, disc_stride, a.T - 1 - it, v_next);
+      acc = s.delta + s.gain * acc;  // :250-253
+      prod *= s.gain;
+      v_next = s.val;
+    }
+  }
+  sh_prod[c][lane] = prod, sh_acc[c][lane] = acc;
+  __syncthreads();
+  if (!live || it0 >= it1) return;
+  float acc_in = 0.0f;
+  for (int k = 0; k < c; ++k) acc_in = fmaf(sh_prod[k][lane], acc_in, sh_acc[k][lane]);
+
+  // second walk: the sequential recurrence from the value that enters the chunk
+  acc = acc_in;
+  float v_next = it0 == 0 ? a.bootstrap[jj] : __ldg(a.values + (a.T - it0) * cols + jj);
+  float vs_next = it0 == 0 ? v_next : acc_in + v_next;  // :268-269
+#pragma unroll 4
+  for (int it = it0; it < it1; ++it) {
+    const int t = a.T - 1 - it;
+    const IwStep s = iw_load(a, cols, jj, rho_col, rho_stride, disc_col, disc_stride, t, v_next);
+    acc = s.delta + s.gain * acc;
+    const float vs = acc + s.val;                                    // :265
+    a.vs[t * cols + jj] = vs;
+    a.pg[t * cols + jj] = s.rho_pg * (s.rew + s.disc * vs_next - s.val);  // :275-276
+    v_next = s.val;
     vs_next = vs;
   }
 }
@@ -177,6 +263,108 @@ __global__ void __launch_bounds__(128) row_kernel(const __grid_constant__ RowArg
   }
 }
 
+// The same five row operations for the action counts the fused kernels are
+// specialised for, with the row arithmetic of vtrace_math.cuh.  A tile of 128
+// rows is 128*A contiguous floats: it arrives with ONE TMA bulk copy
+// (cp.async.bulk -> mbarrier), every thread pulls its row into registers with
+// vector loads (row stride A words: conflict-free for the widths used), and
+// the backward variants write the gradient rows back into the tile, which
+// leaves with one bulk store.  Per row that is a third of the instructions of
+// the generic kernel above, which stays for every other A, for tensors that
+// are not 16-byte aligned and for a ragged last tile.
+template <int MODE, int A_CT>
+__global__ void __launch_bounds__(128) row_tile_kernel(const __grid_constant__ RowArgs a) {
+  __shared__ __align__(128) float tile[128 * A_CT];
+  __shared__ __align__(8) unsigned long long sh_bar;
+  __shared__ double sh_red[128];
+  const int tid = threadIdx.x;
+  const long row0 = static_cast<long>(blockIdx.x) * 128;
+  const int nrows = static_cast<int>(min(128L, a.rows - row0));
+  const int nelem = nrows * A_CT;
+  const uint32_t bytes = static_cast<uint32_t>(nelem) * 4u;
+  const float* src = a.logits + row0 * A_CT;
+  const bool bulk = bytes % 16u == 0;  // a ragged last tile may not be
+  const uint32_t bar = ptx::smem_u32(&sh_bar);
+  if (bulk) {
+    if (tid == 0) {
+      ptx::mbar_init(bar, 1);
+      ptx::fence_mbar_init();
+      ptx::fence_proxy_async();
+      ptx::mbar_arrive_expect_tx(bar, bytes);
+      ptx::bulk_g2s(ptx::smem_u32(tile), src, bytes, bar, ptx::policy_evict_first());
+    }
+  } else {
+    for (int i = tid; i < nelem; i += 128) tile[i] = __ldg(src + i);
+  }
+  // the per-row operands travel while the tile does
+  const long row = row0 + tid;
+  const bool live = tid < nrows;
+  int act = 0;
+  float adv = 0.0f, g = 0.0f;
+  if (live) {
+    if (MODE == kLogProbs || MODE == kPgFwd || MODE == kPgBwd) act = min(max(__ldg(a.actions + row), 0), A_CT - 1);
+    if (MODE == kPgFwd || MODE == kPgBwd) adv = __ldg(a.advantages + row);
+    if (MODE == kPgBwd || MODE == kEntBwd) g = __ldg(a.grad_out);
+  }
+  __syncthreads();  // the barrier is initialised / the plain loads have landed
+  if (bulk) ptx::mbar_wait(bar, 0);
+
+  double partial = 0.0;
+  if (live) {
+    float* mine = tile + tid * A_CT;
+    float x[A_CT];
+    load_row(x, mine);
+    if (MODE == kLogProbs || MODE == kPgFwd) {
+      const math::RowStats st = math::row_stats(x);
+      const float lp = math::action_log_prob(mine[act], st);  // vtrace.py:67
+      if (MODE == kLogProbs) a.out[row] = lp;
+      // cross_entropy * advantages, experiment.py:339-342
+      if (MODE == kPgFwd) partial = -static_cast<double>(lp) * static_cast<double>(adv);
+    } else {
+      float e[A_CT];
+      const math::RowStats st = math::row_stats(x, e);
+      const float inv = __frcp_rn(st.sum);
+      if (MODE == kPgBwd) {  // g adv (softmax - onehot)
+        const float ga = __fmul_rn(g, adv);
+        const float k = __fmul_rn(ga, inv);
+#pragma unroll
+        for (int i = 0; i < A_CT; ++i) e[i] = __fmul_rn(k, e[i]);
+        store_row(mine, e);
+        mine[act] = __fsub_rn(mine[act], ga);
+      } else {
+        const float h = math::row_entropy(x, e, st, inv);          // x <- log-softmax
+        if (MODE == kEntFwd) partial = -static_cast<double>(h);  // experiment.py:334-335
+        if (MODE == kEntBwd) {                                     // g p (log p + H)
+          const float k = __fmul_rn(g, inv);
+#pragma unroll
+          for (int i = 0; i < A_CT; ++i) e[i] = __fmul_rn(__fmul_rn(k, e[i]), __fadd_rn(x[i], h));
+          store_row(mine, e);
+        }
+      }
+    }
+  }
+
+  if (MODE == kPgFwd || MODE == kEntFwd) {
+    const double total = block_sum_fixed(partial, sh_red);
+    if (tid == 0) a.partials[blockIdx.x] = total;
+  }
+  if (MODE == kPgBwd || MODE == kEntBwd) {
+    float* dst = a.out + row0 * A_CT;
+    if (bulk) {
+      ptx::fence_proxy_async();
+      __syncthreads();
+      if (tid == 0) {
+        ptx::bulk_s2g(dst, ptx::smem_u32(tile), bytes);
+        ptx::bulk_commit();
+        ptx::bulk_wait_read<0>();  // the tile is read before the block goes away
+      }
+    } else {
+      __syncthreads();
+      for (int i = tid; i < nelem; i += 128) dst[i] = tile[i];
+    }
+  }
+}
+
 // Second stage for the single-scalar losses: out = scale * sum(partials).
 __global__ void __launch_bounds__(256) reduce_scalar_kernel(const double* __restrict__ partials,
                                                             long n, double scale,
@@ -235,8 +423,29 @@ static long row_blocks(long rows, int A) {
   return (rows + R - 1) / R;
 }
 
+template <int MODE, int A_CT>
+static int launch_row_tiles(const RowArgs& a, cudaStream_t stream) {
+  const long blocks = (a.rows + 127) / 128;
+  if (blocks > 0x7fffffffL) return fail(VTR_ERR_UNSUPPORTED, "too many rows (%ld)", a.rows);
+  row_tile_kernel<MODE, A_CT><<<static_cast<unsigned>(blocks), 128, 0, stream>>>(a);
+  VTR_CUDA_CHECK(cudaGetLastError());
+  return VTR_OK;
+}
+
 template <int MODE>
 static int launch_rows(RowArgs a, cudaStream_t stream) {
+  // compiled-in action counts, 16-byte aligned tensors: the bulk-copy kernel
+  const bool writes_rows = MODE == kPgBwd || MODE == kEntBwd;
+  if (aligned(a.logits, 16) && (!writes_rows || aligned(a.out, 16)) && !getenv("VTR_ROWS_GENERIC")) {
+    switch (a.A) {
+      case 3: return launch_row_tiles<MODE, 3>(a, stream);
+      case 4: return launch_row_tiles<MODE, 4>(a, stream);
+      case 6: return launch_row_tiles<MODE, 6>(a, stream);
+      case 9: return launch_row_tiles<MODE, 9>(a, stream);
+      case 18: return launch_row_tiles<MODE, 18>(a, stream);
+      default: break;
+    }
+  }
   const int R = rows_per_block(a.A);
   a.stride = a.A | 1;
   const size_t smem = static_cast<size_t>(R) * a.stride * sizeof(float);
@@ -290,6 +499,18 @@ extern "C" int vtr_from_importance_weights_f32(const float* log_rhos, const floa
   a.no_clip_pg = (flags & VTR_FLAG_NO_CLIP_PG_RHO) != 0;
   a.clip_rho = clip_rho_threshold, a.clip_pg = clip_pg_rho_threshold;
   const long cols = static_cast<long>(B) * C;
+  // Up to a few hundred thousand columns the unroll is split over the threads
+  // of a block (one thread per column would leave the SMs short of loads in
+  // flight); beyond, one thread per column fills the GPU by itself.
+  vtr::DeviceInfo dev;
+  if (int rc = vtr::device_info(&dev)) return rc;
+  if (T >= 2 * vtr::kIwChunks && cols <= 2048L * dev.sm_count && !getenv("VTR_IW_PLAIN")) {
+    const long blocks = (cols + 31) / 32;
+    vtr::importance_weights_chunk_kernel<<<static_cast<unsigned>(blocks), 32 * vtr::kIwChunks, 0,
+                                           static_cast<cudaStream_t>(stream)>>>(a);
+    VTR_CUDA_CHECK(cudaGetLastError());
+    return VTR_OK;
+  }
   const long blocks = (cols + 127) / 128;
   if (blocks > 0x7fffffffL) return fail(VTR_ERR_UNSUPPORTED, "too many columns");
   vtr::importance_weights_kernel<<<static_cast<unsigned>(blocks), 128, 0,
