@@ -26,6 +26,25 @@
  *   - Pointers documented "may be NULL" switch the corresponding output off.
  *   - Out-of-range actions are clamped to [0, A-1] for memory safety; the
  *     results for such steps are unspecified (TF raises on CPU, vtrace.py:67).
+ *
+ * State the library keeps between calls (device memory compiled into the
+ * library, per GPU; none of it can change a result)
+ *   - Counter sets for the fused pass: 512 sets of 256 uint32, zero at load.
+ *     A launch that finishes its loss reduction in the kernel takes the next
+ *     of 256 sets in turn (tile cursor and tickets of the per-SM kernel, the
+ *     "who finished last" ticket of the others) and its last CTA sets it back
+ *     to zero, so no call needs a memset.  A set comes round again 256 fused
+ *     calls later: keep fewer than 256 fused calls pending per GPU.  A call
+ *     captured into a CUDA graph keeps one of the other 256 sets for good;
+ *     once those are used up, captured calls zero counters in the workspace
+ *     header (memset node) or leave the last stage to a second launch.
+ *   - The per-SM speed table of the per-SM kernel (VTR_PATH_SM_TILE): each
+ *     tile records how fast its SM streamed, the next call sizes its tiles
+ *     from that.  Only the partition of the batch depends on it; every output
+ *     is independent of the partition.  Concurrent callers on two streams
+ *     update it without synchronisation; the worst that can happen is a less
+ *     even partition on the next call.
+ *   - The 200 KiB array of vtr_from_logits_fused_noalloc_f32 (see there).
  */
 #ifndef VTRACE_B200_H_
 #define VTRACE_B200_H_
@@ -60,8 +79,11 @@ extern "C" {
 #define VTR_PATH_AUTO 0
 #define VTR_PATH_COLUMN 1  /* 32-column tiles, one ring per tile (any alignment) */
 #define VTR_PATH_SM_TILE 2 /* one wide tile per SM, shared ring (16-B aligned)  */
-#define VTR_PATH_ITEM 3    /* one thread per (t, b) item: small B, T <= 256      */
-#define VTR_PATH_CHUNK 4   /* T split over a thread-block cluster: mid-sized B   */
+#define VTR_PATH_ITEM 3    /* one thread per (t, b) item, warp-shuffle affine scan
+                              over T: tiny B, T <= 256, compiled-in A            */
+#define VTR_PATH_CHUNK 4   /* T split over a thread-block cluster, chunk aggregates
+                              of the recurrence through distributed shared
+                              memory: small and mid-sized B, T <= 104            */
 
 int vtr_version(void);
 
@@ -71,7 +93,7 @@ const char* vtr_last_error(void);
 /*
  * Arguments of the fused forward+backward pass.
  *
- * Replaces, in one launch (plus one tiny reduction launch):
+ * Replaces, in one launch:
  *   vtrace.from_logits                        vtrace.py:71-161
  *     log_probs_from_logits_and_actions x2    vtrace.py:45-68, 143-146
  *     from_importance_weights                 vtrace.py:164-280
@@ -160,11 +182,13 @@ typedef struct vtr_fused_params {
   float* total_loss;
 } vtr_fused_params;
 
-/* Bytes of device workspace vtr_from_logits_fused_f32 needs for (T,B,A): an
-   8 KB header (tile cursor, tickets and group partials of the per-SM kernel;
-   the library zeroes what must be zero itself) followed by the loss partials
-   of the deterministic staged reduction, one double[3] per 32-column tile,
-   per 4-column granule or per column depending on the kernel.  Returns 0 on
+/* Bytes of device workspace that are enough for vtr_from_logits_fused_f32 at
+   (T,B,A) whichever kernel runs: an 8 KB header (group partials of the per-SM
+   kernel; counters only in the fallback described above, which the library
+   zeroes itself) followed by the loss partials of the deterministic staged
+   reduction, one double[3] per 32-column tile, per 4-column granule, per
+   column or per CTA depending on the kernel.  The call itself checks against
+   what the kernel it picks really writes, which can be less.  Returns 0 on
    invalid sizes. */
 size_t vtr_fused_workspace_bytes(int32_t T, int32_t B, int32_t A);
 
