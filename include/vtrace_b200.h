@@ -380,6 +380,29 @@ int vtr_rmsprop_allreduce_f32(void* const* var_peers, void* const* grad_peers, v
 void vtr_set_peer_timeout_ms(uint64_t milliseconds);
 uint64_t vtr_get_peer_timeout_ms(void);
 
+/*
+ * The policy and baseline heads that produce the path's inputs
+ * (experiment.py:199-203: snt.Linear(num_actions) and snt.Linear(1) on the
+ * core output, applied over [T*B, K] by snt.BatchApply at :237; K = 256):
+ *   policy_logits[r, a] = sum_k core_output[r, k] w_policy[k, a] + b_policy[a]
+ *   baseline[r]         = sum_k core_output[r, k] w_baseline[k]  + b_baseline
+ * One tensor-core kernel (tcgen05.mma, accumulators in TMEM, tensor-map TMA
+ * loads), fp32-accurate: every product is formed as three TF32 products of
+ * the operands' high and low halves, so the logits are good to ~1e-6 and the
+ * V-trace outputs computed from them keep their 1e-5 bound.
+ * K must be a multiple of 32 up to 256 and A at most 31.  The weights are
+ * packed once per update (w_policy [K, A] as Sonnet stores it, b_policy [A],
+ * w_baseline [K], b_baseline [1]) into `packed`, a 128-byte aligned device
+ * buffer of vtr_policy_head_packed_bytes(K, A) bytes; core_output is [rows, K],
+ * 16-byte aligned; policy_logits [rows, A] and baseline [rows] are laid out as
+ * the fused pass takes them (rows = T*B, time-major).
+ */
+size_t vtr_policy_head_packed_bytes(int32_t K, int32_t A);
+int vtr_policy_head_prepare_f32(const float* w_policy, const float* b_policy, const float* w_baseline,
+                                const float* b_baseline, int32_t K, int32_t A, void* packed, void* stream);
+int vtr_policy_head_f32(const float* core_output, const void* packed, int64_t rows, int32_t K, int32_t A,
+                        float* policy_logits, float* baseline, void* stream);
+
 /* x[i] *= *scale for i < n, skipped entirely when *scale == 1.  `scale` is a
    device float[1].  Used to apply the upstream gradient of the total loss
    (experiment.py:415) to the gradients the fused pass already produced,

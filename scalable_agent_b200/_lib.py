@@ -109,6 +109,9 @@ SIGNATURES = {
         (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
                         ctypes.POINTER(ctypes.c_void_p), _P, _P, _I64, _I32, _I32, _U32,
                         _F, _F, _F, _F, _P, _P]),
+    'vtr_policy_head_packed_bytes': (_SZ, [_I32, _I32]),
+    'vtr_policy_head_prepare_f32': (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P]),
+    'vtr_policy_head_f32': (ctypes.c_int, [_P, _P, _I64, _I32, _I32, _P, _P, _P]),
     'vtr_set_peer_timeout_ms': (None, [ctypes.c_uint64]),
     'vtr_get_peer_timeout_ms': (ctypes.c_uint64, []),
 }
