@@ -10,25 +10,35 @@
 //
 // tcgen05 kernel, one persistent CTA per SM, roles by warp:
 //   warps 0-3  epilogue   TMEM -> registers (tcgen05.ld), + bias, -> HBM
-//   warps 4-7  splitters  fp32 tile -> (hi, lo) TF32 halves, in shared memory
+//   warps 4-7  splitters  a thread pulls its row of the landed fp32 tile out of
+//                         shared memory, splits it into (hi, lo) TF32 halves and
+//                         stores them into TENSOR MEMORY (tcgen05.st)
 //   warp  8    producer   TMA tensor-map loads (cp.async.bulk.tensor) of the
 //                         core-output tiles into a ring, 128B-swizzled
-//   warp  9    MMA        one elected lane issues tcgen05.mma.kind::tf32,
-//                         accumulators in TMEM, completion by tcgen05.commit
+//   warp  9    MMA        one elected lane issues tcgen05.mma.kind::tf32 with
+//                         the A operand in TMEM and the weights in shared
+//                         memory, accumulators in TMEM, completion by
+//                         tcgen05.commit
+// The A operand goes through TMEM, not shared memory, because shared-memory
+// bandwidth is what bounded the first version (A halves written to and read
+// back from shared memory by three MMAs per k-step: 124 KB of shared-memory
+// traffic per 16 KB landed, 3.9 us per tile against 2.9 us of HBM time; 902 us
+// at T*B = 3.3 M rows).  Now a landed tile is read from shared memory once.
 // Precision: the V-trace outputs are held to 1e-5 of a float64 oracle and the
 // logits feed them, so one TF32 pass (10-bit mantissa) is not enough.  Each
 // operand is split x = hi + lo with hi = x with the low 13 mantissa bits
 // cleared (exactly what a TF32 multiplier keeps) and lo = x - hi (exact), and
-// the product is accumulated as hi*hi + hi*lo + lo*hi in fp32 in TMEM ("3xTF32":
-// the dropped lo*lo term and the truncation of the lo parts are 2^-22 relative).
+// the product is accumulated as hi*hi + hi*lo + lo*hi + lo*lo in fp32 in TMEM
+// (the "3xTF32" scheme plus the fourth term, which comes for free here; what is
+// left is the truncation of the lo parts, 2^-22 relative).
 // The tensor core's fp32 accumulation does not round to nearest - a chain of 96
 // accumulations into one accumulator came out 1.5e-6 low on sums of magnitude 2,
-// with the same sign everywhere - so every k-block of 32 has an accumulator of
-// its own (12 accumulations each) and the epilogue adds the 8 of them in
-// registers with round-to-nearest.
+// with the same sign everywhere - so a tile has four accumulators, one per
+// k-step of a k-block (8 to 16 accumulations each), and the epilogue adds them
+// in registers with round-to-nearest.  Spreading consecutive MMAs over
+// different accumulators is also what lets the tensor pipe overlap them.
 // The weights are split once (vtr_policy_head_prepare_f32); the activations are
-// split tile by tile in shared memory, which is layout-agnostic because the
-// split is elementwise.
+// split on their way from shared memory to tensor memory.
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -43,13 +53,23 @@ constexpr int kTileN = 32;           // accumulator columns: A + 1 <= 32
 constexpr int kBlockK = 32;          // fp32 elements per 128-byte swizzled row
 constexpr int kUmmaK = 8;            // K of one tcgen05.mma.kind::tf32
 constexpr int kMaxK = 256;
-constexpr int kStages = 4;           // ring of core-output tiles
-constexpr int kAccStages = 2;        // tiles' accumulators in flight
-constexpr int kAccCols = (kMaxK / kBlockK) * kTileN;  // one 32-column accumulator per k-block: 256 columns
-constexpr int kTmemCols = kAccStages * kAccCols;      // 512: all of an SM's tensor memory
+constexpr int kStages = 8;           // ring of landed core-output tiles (16 KB each)
+constexpr int kAccStages = 1;        // tiles' accumulators in flight (the epilogue drains them in ~0.3 us)
+constexpr int kAccSets = kBlockK / kUmmaK;  // 4 accumulators per tile: k-step kk of every k-block goes to set kk
+constexpr int kAccN = 2 * kTileN;    // an accumulator: 32 columns of hi*hi, 32 of the two small terms
+constexpr int kAccCols = kAccSets * kAccN;  // 4 x 64 columns per tile
+// (hi, lo) A operands in tensor memory, 64 columns each.  Their number is what
+// sets the pace: a buffer is busy from the splitters' tcgen05.st to the commit
+// of the MMAs that read it, a round trip of ~3.5k cycles; with 3 buffers the
+// kernel ran at one k-block per 1150 cycles (0.61 of the copy bandwidth), the
+// splitters waiting for a free buffer a quarter of the time.  (More buffers
+// did not help: see the note on the MMA count at the issue loop.)
+constexpr int kABufs = 4;
+constexpr int kABase = kAccStages * kAccCols;                     // columns [256, 512)
+constexpr int kTmemCols = 512;       // all of an SM's tensor memory (power of two)
 constexpr int kThreads = 320;
 constexpr int kStageBytes = kTileM * kBlockK * 4;   // 16 KB
-constexpr int kWBlockBytes = kTileN * kBlockK * 4;  // 4 KB
+constexpr int kWBlockBytes = kTileN * kBlockK * 4;  // 4 KB: [32 n][32 k] of W_hi, then the same of W_lo
 constexpr unsigned long long kWatchdogNs = 4000000000ull;  // a wait this long is a bug: trap, do not hang
 
 struct HeadArgs {
@@ -59,16 +79,17 @@ struct HeadArgs {
   long rows;
   int K, A;
   int num_tiles;
+  int terms;  // 3; experiments: 1 = hi*hi only (TF32 accuracy), 0 = no MMA at all
 };
 
 // Shared memory, 1024-byte aligned (the 128B swizzle atom is 8 rows x 128 B):
-//   a_hi  kStages x 16 KB   core tile as loaded, then its hi half
-//   a_lo  kStages x 16 KB   lo half
+//   raw   kStages x 16 KB   core tiles as they land ([128 rows][32 k], 128B-swizzled)
 //   w_hi  (K/32) x 4 KB     weights^T [32 n][32 k] per k-block, hi / lo
 //   w_lo  (K/32) x 4 KB
 //   barriers, TMEM base address, bias
 struct Barriers {
-  unsigned long long full[kStages], split[kStages], empty[kStages];
+  unsigned long long full[kStages], empty[kStages];      // landed tile: TMA -> splitters -> producer
+  unsigned long long a_full[kABufs], a_empty[kABufs];    // A operand in TMEM: splitters -> MMA -> splitters
   unsigned long long acc_full[kAccStages], acc_empty[kAccStages];
   unsigned long long weights;
   uint32_t tmem_base;
@@ -76,7 +97,7 @@ struct Barriers {
 };
 
 static size_t smem_bytes(int K) {
-  return 1024 + 2u * kStages * kStageBytes + 2u * (K / kBlockK) * kWBlockBytes + sizeof(Barriers);
+  return 1024 + kStages * kStageBytes + 2u * (K / kBlockK) * kWBlockBytes + sizeof(Barriers);
 }
 
 // ---- PTX ---------------------------------------------------------------------
@@ -122,6 +143,42 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t desc_a, uint6
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same with the A operand in tensor memory (lane = row, one column per k).
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 columns from the warp's registers into tensor memory.
+__device__ __forceinline__ void tmem_store_32x32(uint32_t addr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(addr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
+      "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
+      "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_store_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 // Arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed.
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -153,8 +210,11 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t byte_offse
   d |= static_cast<uint64_t>(2) << 61;            // SWIZZLE_128B
   return d;
 }
-// Instruction descriptor: fp32 accumulator, TF32 A and B, both K-major, N = 32, M = 128.
-constexpr uint32_t kInstrDesc = (1u << 4) | (2u << 7) | (2u << 10) | ((kTileN >> 3) << 17) | ((kTileM >> 4) << 24);
+// Instruction descriptor: fp32 accumulator, TF32 A and B, both K-major, M = 128, N = 32 or 64.
+constexpr uint32_t instr_desc(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(n >> 3) << 17) | ((kTileM >> 4) << 24);
+}
+constexpr uint32_t kInstrDesc64 = instr_desc(2 * kTileN);
 
 // ---- the kernel --------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
@@ -165,18 +225,19 @@ __global__ void __launch_bounds__(kThreads, 1)
   unsigned char* smem = reinterpret_cast<unsigned char*>(
       (reinterpret_cast<uintptr_t>(smem_unaligned) + 1023) & ~static_cast<uintptr_t>(1023));
   const int num_kb = a.K / kBlockK;
-  unsigned char* a_hi = smem;
-  unsigned char* a_lo = a_hi + kStages * kStageBytes;
-  unsigned char* w_hi = a_lo + kStages * kStageBytes;
-  unsigned char* w_lo = w_hi + num_kb * kWBlockBytes;
-  Barriers* bars = reinterpret_cast<Barriers*>(w_lo + num_kb * kWBlockBytes);
+  unsigned char* raw = smem;
+  unsigned char* w_cat = raw + kStages * kStageBytes;  // per k-block 8 KB: [W_hi rows 0-31 | W_lo rows 32-63] x 32 k
+  Barriers* bars = reinterpret_cast<Barriers*>(w_cat + 2 * num_kb * kWBlockBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(ptx::smem_u32(&bars->full[s]), 1);
-      ptx::mbar_init(ptx::smem_u32(&bars->split[s]), 4);   // one arrival per splitter warp
-      ptx::mbar_init(ptx::smem_u32(&bars->empty[s]), 1);   // tcgen05.commit
+      ptx::mbar_init(ptx::smem_u32(&bars->empty[s]), 4);  // one arrival per splitter warp
+    }
+    for (int j = 0; j < kABufs; ++j) {
+      ptx::mbar_init(ptx::smem_u32(&bars->a_full[j]), 4);   // one arrival per splitter warp
+      ptx::mbar_init(ptx::smem_u32(&bars->a_empty[j]), 1);  // tcgen05.commit
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(ptx::smem_u32(&bars->acc_full[s]), 1);   // tcgen05.commit
@@ -204,8 +265,8 @@ __global__ void __launch_bounds__(kThreads, 1)
       const uint32_t wbar = ptx::smem_u32(&bars->weights);
       ptx::mbar_arrive_expect_tx(wbar, 2u * num_kb * kWBlockBytes);
       for (int kb = 0; kb < num_kb; ++kb) {
-        tma_load_2d(ptx::smem_u32(w_hi + kb * kWBlockBytes), &map_w_hi, kb * kBlockK, 0, wbar);
-        tma_load_2d(ptx::smem_u32(w_lo + kb * kWBlockBytes), &map_w_lo, kb * kBlockK, 0, wbar);
+        tma_load_2d(ptx::smem_u32(w_cat + 2 * kb * kWBlockBytes), &map_w_hi, kb * kBlockK, 0, wbar);
+        tma_load_2d(ptx::smem_u32(w_cat + (2 * kb + 1) * kWBlockBytes), &map_w_lo, kb * kBlockK, 0, wbar);
       }
       int it = 0;
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
@@ -214,67 +275,93 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (use > 0) wait_or_trap(ptx::smem_u32(&bars->empty[s]), (use - 1) & 1);
           const uint32_t bar = ptx::smem_u32(&bars->full[s]);
           ptx::mbar_arrive_expect_tx(bar, kStageBytes);
-          tma_load_2d(ptx::smem_u32(a_hi + s * kStageBytes), &map_core, kb * kBlockK, tile * kTileM, bar);
+          tma_load_2d(ptx::smem_u32(raw + s * kStageBytes), &map_core, kb * kBlockK, tile * kTileM, bar);
         }
       }
     }
   } else if (warp >= 4 && warp < 8) {
-    // ===== splitters: x -> hi (low 13 mantissa bits cleared, in place) and lo = x - hi =====
-    const int tid = threadIdx.x - 128;
+    // ===== splitters: thread = row.  x -> hi (low 13 mantissa bits cleared) and lo = x - hi,
+    // from the landed tile in shared memory into the A operand in tensor memory =====
+    const int q = warp - 4;              // the warp's quarter of the TMEM lanes
+    const int row = 32 * q + lane;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(32 * q) << 16);
     int it = 0;
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
-        const int s = it % kStages, use = it / kStages;
-        wait_or_trap(ptx::smem_u32(&bars->full[s]), use & 1);
-        float4* hi = reinterpret_cast<float4*>(a_hi + s * kStageBytes);
-        float4* lo = reinterpret_cast<float4*>(a_lo + s * kStageBytes);
+        const int s = it % kStages, j = it % kABufs;
+        wait_or_trap(ptx::smem_u32(&bars->full[s]), (it / kStages) & 1);
+        // A row is 128 bytes = 8 chunks of 16; chunk c sits at position c ^ (row % 8) (128B swizzle),
+        // which is also what makes 8 neighbouring rows hit different banks.
+        const float4* src = reinterpret_cast<const float4*>(raw + s * kStageBytes + row * 128);
+        uint32_t hi[32], lo[32];
 #pragma unroll
-        for (int j = 0; j < kStageBytes / 16 / 128; ++j) {
-          const int i = tid + 128 * j;
-          const float4 x = hi[i];
-          float4 h, l;
-          h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u), l.x = __fsub_rn(x.x, h.x);
-          h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u), l.y = __fsub_rn(x.y, h.y);
-          h.z = __uint_as_float(__float_as_uint(x.z) & 0xffffe000u), l.z = __fsub_rn(x.z, h.z);
-          h.w = __uint_as_float(__float_as_uint(x.w) & 0xffffe000u), l.w = __fsub_rn(x.w, h.w);
-          hi[i] = h, lo[i] = l;
+        for (int c = 0; c < 8; ++c) {
+          const float4 x = src[c ^ (row & 7)];
+          const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t h = __float_as_uint(xs[e]) & 0xffffe000u;
+            hi[4 * c + e] = h;
+            lo[4 * c + e] = __float_as_uint(__fsub_rn(xs[e], __uint_as_float(h)));
+          }
         }
-        ptx::fence_proxy_async();  // these generic-proxy writes are read by the tensor core (async proxy)
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->split[s]));
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->empty[s]));  // the landed tile is in registers
+        if (it >= kABufs) wait_or_trap(ptx::smem_u32(&bars->a_empty[j]), ((it / kABufs) - 1) & 1);
+        tc_fence_after();
+        const uint32_t dst = lane_base + static_cast<uint32_t>(kABase + 64 * j);
+        tmem_store_32x32(dst, hi);
+        tmem_store_32x32(dst + 32, lo);
+        tmem_store_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&bars->a_full[j]));
       }
     }
   } else if (warp == 9) {
-    // ===== MMA issuer: one lane, 3 x TF32 per k-step into the tile's accumulator =====
-    if (lane == 0) {
-      wait_or_trap(ptx::smem_u32(&bars->weights), 0);
-      int it = 0, local_tile = 0;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++local_tile) {
-        const int acc = local_tile % kAccStages, acc_use = local_tile / kAccStages;
-        if (acc_use > 0) wait_or_trap(ptx::smem_u32(&bars->acc_empty[acc]), (acc_use - 1) & 1);
+    // ===== MMA issuer: A from tensor memory, weights from shared memory =====
+    // The whole warp walks the loop (waits, addresses: warp-uniform values, cheap) and one elected
+    // lane issues.  The instruction stream of this one warp was the bottleneck of earlier versions:
+    // ~180 instructions per k-block around 12 MMAs, with every operand re-derived and moved to the
+    // uniform registers behind an election, is ~1150 cycles - more than the 830 the HBM stream
+    // leaves per k-block - while the tensor pipe itself was mostly idle (0.61 of the copy bandwidth
+    // then, 0.90 with the MMAs switched off).
+    wait_or_trap(ptx::smem_u32(&bars->weights), 0);
+    const uint64_t wdesc0 = smem_desc(ptx::smem_u32(w_cat), 0);
+    int it = 0, local_tile = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++local_tile) {
+      const int acc = local_tile % kAccStages, acc_use = local_tile / kAccStages;
+      if (acc_use > 0) wait_or_trap(ptx::smem_u32(&bars->acc_empty[acc]), (acc_use - 1) & 1);
+      const uint32_t d0 = tmem_base + static_cast<uint32_t>(acc * kAccCols);
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int j = it % kABufs;
+        wait_or_trap(ptx::smem_u32(&bars->a_full[j]), (it / kABufs) & 1);
         tc_fence_after();
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const uint32_t d = tmem_base + static_cast<uint32_t>(acc * kAccCols + kb * kTileN);
-          const int s = it % kStages, use = it / kStages;
-          wait_or_trap(ptx::smem_u32(&bars->split[s]), use & 1);
-          tc_fence_after();
-          const uint32_t ah = ptx::smem_u32(a_hi + s * kStageBytes), al = ptx::smem_u32(a_lo + s * kStageBytes);
-          const uint32_t wh = ptx::smem_u32(w_hi + kb * kWBlockBytes), wl = ptx::smem_u32(w_lo + kb * kWBlockBytes);
+        const uint32_t ah = tmem_base + static_cast<uint32_t>(kABase + 64 * j);
+        // descriptor of k-block kb: the start address field moves by 8 KB (in 16-byte units)
+        const uint64_t wd = wdesc0 + static_cast<uint64_t>(kb * (2 * kWBlockBytes >> 4));
+        // Two MMAs per k-step of 8, both M128 x N64 x K8 against B = [W_hi | W_lo]: A_hi gives hi*hi in
+        // columns 0-31 of the accumulator and hi*lo in 32-63, A_lo adds lo*hi and lo*lo on top - all
+        // four partial products in two instructions.  Never two in a row into the same accumulator
+        // (back-to-back MMAs on the same TMEM columns wait for each other): k-step kk accumulates
+        // into set kk, and the four A_lo MMAs follow the four A_hi ones.
+        if (elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < kBlockK / kUmmaK; ++kk) {
-            const uint32_t off = kk * kUmmaK * 4;
-            // small terms first: hi*lo and lo*hi, then hi*hi
-            mma_tf32(d, smem_desc(ah, off), smem_desc(wl, off), kInstrDesc, kk != 0);
-            mma_tf32(d, smem_desc(al, off), smem_desc(wh, off), kInstrDesc, 1);
-            mma_tf32(d, smem_desc(ah, off), smem_desc(wh, off), kInstrDesc, 1);
-          }
-          mma_commit(ptx::smem_u32(&bars->empty[s]));  // the stage is free once these have read it
+          for (int kk = 0; kk < kAccSets; ++kk)
+            if (a.terms >= 1)
+              mma_tf32_ts(d0 + kk * kAccN, ah + kk * kUmmaK, wd + 2 * kk, kInstrDesc64, kb != 0);
+#pragma unroll
+          for (int kk = 0; kk < kAccSets; ++kk)
+            if (a.terms >= 3) mma_tf32_ts(d0 + kk * kAccN, ah + 32 + kk * kUmmaK, wd + 2 * kk, kInstrDesc64, 1);
+          mma_commit(ptx::smem_u32(&bars->a_empty[j]));  // the A operand is free once these have read it
+          if (kb == num_kb - 1) mma_commit(ptx::smem_u32(&bars->acc_full[acc]));  // the tile is complete
         }
-        mma_commit(ptx::smem_u32(&bars->acc_full[acc]));  // the tile's accumulator is complete
+        __syncwarp();
       }
     }
   } else {
     // ===== epilogue: warp w owns TMEM lanes 32w..32w+31 = rows of the tile =====
+    const int num_acc = kAccSets;
     int local_tile = 0;
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++local_tile) {
       const int acc = local_tile % kAccStages, acc_use = local_tile / kAccStages;
@@ -283,10 +370,11 @@ __global__ void __launch_bounds__(kThreads, 1)
       float y[kTileN];
 #pragma unroll
       for (int n = 0; n < kTileN; ++n) y[n] = 0.0f;
-      for (int kb = 0; kb < num_kb; ++kb) {  // the k-blocks' accumulators, added with round-to-nearest
+      for (int g = 0; g < 2 * num_acc; ++g) {  // small terms first (odd halves), then hi*hi; round-to-nearest
+        const int half = g < num_acc ? 1 : 0, which = g < num_acc ? g : g - num_acc;
         uint32_t v[32];
         tmem_load_32x32(tmem_base + (static_cast<uint32_t>(warp * 32) << 16) +
-                            static_cast<uint32_t>(acc * kAccCols + kb * kTileN), v);
+                            static_cast<uint32_t>(acc * kAccCols + which * kAccN + half * kTileN), v);
 #pragma unroll
         for (int n = 0; n < kTileN; ++n) y[n] = __fadd_rn(y[n], __uint_as_float(v[n]));
       }
@@ -297,7 +385,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       if (row < a.rows) {
         float* out = a.logits + row * a.A;
 #pragma unroll
-        for (int n = 0; n < kTileN; ++n) {  // unrolled: v[] stays in registers
+        for (int n = 0; n < kTileN; ++n) {  // unrolled: y[] stays in registers
           const float out_n = __fadd_rn(y[n], bars->bias[n]);
           if (n < a.A) out[n] = out_n;
           else if (n == a.A) a.baseline[row] = out_n;
@@ -429,6 +517,8 @@ extern "C" int vtr_policy_head_f32(const float* core_output, const void* packed,
   a.logits = policy_logits, a.baseline = baseline, a.bias = p + 2 * kTileN * K;
   a.rows = rows, a.K = K, a.A = A;
   a.num_tiles = static_cast<int>((rows + kTileM - 1) / kTileM);
+  a.terms = 3;
+  if (const char* v = getenv("VTR_HEAD_TERMS")) a.terms = atoi(v);  // experiments only
   const size_t smem = smem_bytes(K);
   if (int rc = vtr::allow_dynamic_smem(reinterpret_cast<const void*>(policy_head_kernel), smem)) return rc;
   const int grid = a.num_tiles < dev.sm_count ? a.num_tiles : dev.sm_count;
