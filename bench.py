@@ -267,6 +267,64 @@ class FusedCall(object):
       self._lib_mod.check(rc, 'vtr_from_logits_fused_f32')
 
 
+def time_heads(T, B, A, call, device, steps):
+  """The heads kernel at rows = T*B, K = 256 (the reference's core width):
+  HBM-bound, 4K bytes read + 4(A+1) written per row."""
+  import torch
+  from scalable_agent_b200 import _lib, heads
+  lib = _lib.load()
+  Kc, rows = 256, T * B
+  g = torch.Generator(device=device).manual_seed(99)
+  core = torch.randn(rows, Kc, generator=g, device=device)
+  packed = heads.pack_head_weights(
+      torch.randn(Kc, A, generator=g, device=device) / 16, torch.zeros(A, device=device),
+      torch.randn(Kc, generator=g, device=device) / 16, torch.zeros(1, device=device))
+  logits = torch.empty(rows, A, device=device)
+  baseline = torch.empty(rows, device=device)
+  stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+  def head():
+    rc = lib.vtr_policy_head_f32(core.data_ptr(), packed.data_ptr(), rows, Kc, A,
+                                 logits.data_ptr(), baseline.data_ptr(), stream)
+    if rc != 0:
+      _lib.check(rc, 'vtr_policy_head_f32')
+
+  def timed(fn, n):
+    for _ in range(3):
+      fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+      fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / n
+
+  n = max(5, min(steps, 30))
+  head_ms = timed(head, n)
+  saved = (call.p.target_policy_logits, call.p.values)
+  call.p.target_policy_logits, call.p.values = logits.data_ptr(), baseline.data_ptr()
+
+  def block():
+    head()
+    call()
+  block_ms = timed(block, n)
+  call.p.target_policy_logits, call.p.values = saved
+  peak, _ = measured_peak_gbs()
+  nbytes = rows * (4 * Kc + 4 * (A + 1)) + 4 * Kc * (A + 1)
+  achieved = nbytes / (head_ms * 1e-3) / 1e9
+  return {
+      'workload': 'policy + baseline heads (experiment.py:199-203), [T*B=%d, %d] x [%d, %d], fp32-accurate '
+                  '(3xTF32 tcgen05 kernel)' % (rows, Kc, Kc, A + 1),
+      'ms_per_step': head_ms, 'rows_per_s': rows / (head_ms * 1e-3),
+      'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                   'frac': achieved / peak, 'algorithmic_bytes_per_launch': nbytes},
+      'block_ms_per_step': block_ms,
+      'block': 'heads kernel + fused V-trace/loss pass, back to back on one stream',
+      'block_timesteps_per_s': rows / (block_ms * 1e-3)}
+
+
 def run_gpu(args):
   import torch
   import torch.distributed as dist
@@ -476,6 +534,17 @@ def run_gpu(args):
              'device-resident inputs, CUDA events'}
   del api_in
 
+  # ---- the heads upstream of the path (experiment.py:199-203) ---------------
+  # A second shape with a roofline of its own: [T*B, 256] x [256, A+1] on the
+  # tcgen05 kernel, alone and in front of the fused pass (1 GPU only: it reads
+  # 3.4 GB of core output at the headline shape).
+  heads_line = None
+  if world == 1 and not args.no_heads:
+    try:
+      heads_line = time_heads(T, B, A, calls[0], device, K)
+    except Exception as e:  # pylint: disable=broad-except
+      heads_line = {'error': str(e).splitlines()[0][:200]}
+
   # ---- end to end through the public API with host buffers ---------------
   e2e_steps = max(1, min(K, 10))
   host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v)
@@ -564,6 +633,7 @@ def run_gpu(args):
                        'backward, pinned host inputs'},
         'api_device': api_device,
         'exchange_check': exchange_check,
+        'heads': heads_line,
         'gpu_launches': (call.launches_per_call +
                          (0 if exchange is None or fused_exchange else 2)) * K,
         'clocks': dict(sampler.summary(), sampled=clock_note),
@@ -601,6 +671,8 @@ def main():
   ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
                   help='weak: --B columns on every GPU; strong: --B columns in all')
   ap.add_argument('--no-cpu-baseline', action='store_true')
+  ap.add_argument('--no-heads', action='store_true',
+                  help='skip the heads-kernel leg (tcgen05 contraction upstream of the path)')
   ap.add_argument('--exchange', default='fused', choices=['fused', 'p2p', 'nccl'],
                   help='how the loss scalars are summed over ranks (N > 1)')
   ap.add_argument('--exchange-lag', type=int, default=1, choices=[0, 1],
