@@ -121,6 +121,11 @@ __global__ void __launch_bounds__(32 * kChunkMaxSteps, (A_CT > 0 && A_CT <= 9) ?
   const bool tma_out = a.tma_out_ok && (row_bytes % 16u == 0);
   const bool need_softmax = GRADS || a.partials != nullptr;
 
+  // Programmatic dependent launch (see launch_config() in vtrace_fused.cu):
+  // no tensor is touched before this point.
+  ptx::grid_launch_dependents();
+  ptx::grid_dependency_wait();
+
   // ---- loads: the two rows through shared memory, the operands directly ----
   // Every warp has its own barrier and waits for nobody else's rows.
   int act = 0;

@@ -40,6 +40,10 @@ __global__ void __launch_bounds__(32) fused_column_kernel(const __grid_constant_
     ptx::fence_proxy_async();
   }
   __syncwarp();
+  // Programmatic dependent launch (launch_config() in vtrace_fused.cu): no
+  // tensor is touched before this point.
+  ptx::grid_launch_dependents();
+  ptx::grid_dependency_wait();
   const uint64_t policy = ptx::policy_evict_first();
 
   auto issue = [&](int t, int s) {

@@ -67,6 +67,10 @@ __global__ void __launch_bounds__(kItemMaxSteps) fused_item_kernel(const __grid_
   const int t = T - 1 - (active ? k : 0);
   const size_t e = static_cast<size_t>(t) * B + b;
   const bool need_softmax = GRADS || a.partials != nullptr;
+  // Programmatic dependent launch (launch_config() in vtrace_fused.cu): no
+  // tensor is touched before this point.
+  ptx::grid_launch_dependents();
+  ptx::grid_dependency_wait();
 
   float disc = 0.0f, rew = 0.0f, val = 0.0f, v_next = 0.0f, t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
   float entropy = 0.0f, inv_sum = 0.0f;

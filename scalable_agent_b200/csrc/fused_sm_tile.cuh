@@ -159,7 +159,6 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   // late tiles find the cursor at B and leave.
   __shared__ int sh_range[3];  // first column, columns, drew the last ticket
   const int total_gran = B >> 2;
-  const unsigned long long t_begin = global_timer_ns();
   if (args.cursor) {
     if (warp == 0) {
       int share = weighted_share(args, total_gran, cols >> 2, lane, sm_id());
@@ -193,7 +192,13 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   const uint32_t carry_bars = full_bars + 256u;
   const uint32_t ring_u32 = ptx::smem_u32(ring);
 
-  int cols_done = 0;
+  // Everything above ran on set-up data only (kernel arguments, the library's
+  // counters and speed table); from here on the tensors are touched.
+  ptx::grid_dependency_wait();
+  // The SM's speed is measured from here: time spent waiting for the previous
+  // kernel says nothing about this SM.
+  const unsigned long long t_begin = global_timer_ns();
+
   for (int pass = 0;; ++pass) {  // one pass, except for the last ticket's leftovers
   if (threadIdx.x == 0) {
     for (int s = 0; s < depth; ++s) {
@@ -389,11 +394,34 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     if (GRADS && lane == 0) ptx::bulk_wait<0>();
   }
 
+  __syncthreads();  // the streaming part of this pass is over
+  if (pass == 0 && threadIdx.x == 0) {
+    const unsigned int sm = sm_id();
+    const unsigned long long dt = global_timer_ns() - t_begin;
+    // Tiles shorter than 20 us measure launch latency, not the SM: leave the table alone.
+    if (ncols > 0 && sm < kMaxSms && dt > 20000) {
+      const float speed = static_cast<float>(ncols) * T / static_cast<float>(dt);
+      // Running mean over the first 1 / smoothing measurements, exponential
+      // after: one tile's time is noisy (+-2 % from call to call on the same
+      // addresses), and noise in the table is imbalance in the next call.
+      const unsigned int n = g_sm_samples[sm] + 1u;
+      const float weight = fmaxf(args.smoothing, 1.0f / static_cast<float>(n));
+      const float old = g_sm_speed[sm];
+      g_sm_speed[sm] = old > 0.0f ? old + weight * (speed - old) : speed;
+      if (n < 1000000u) g_sm_samples[sm] = n;
+      __threadfence();
+    }
+    // The next launch of the stream may now place its tiles; it starts once
+    // every tile of this one has got here, so all of its tiles size
+    // themselves from the same, complete speed table.  What is left of this
+    // launch - the loss reduction - overlaps that set-up.
+    ptx::grid_launch_dependents();
+  }
+
   if (a.partials) {
     // One partial per granule of 4 columns, summed over the relay warps and then
     // over the 4 lanes in a fixed order: the same numbers however the batch
     // was cut into tiles.
-    __syncthreads();
     for (int q = threadIdx.x; q < (ncols >> 2); q += blockDim.x) {
       const int g = (4 * q) >> 5, l0 = (4 * q) & 31;
       double p[3] = {0.0, 0.0, 0.0};
@@ -497,7 +525,6 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
       __syncthreads();
     }
   }
-  cols_done += ncols;
   if (!sh_range[2] || col0 + ncols >= B) break;
   __syncthreads();  // everybody is done with this pass's range and barriers
   if (threadIdx.x == 0) {
@@ -505,22 +532,6 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     sh_range[1] = min(cols, B - (col0 + ncols));
   }
   }  // pass
-  if (threadIdx.x == 0 && cols_done > 0) {
-    const unsigned int sm = sm_id();
-    const unsigned long long dt = global_timer_ns() - t_begin;
-    // Tiles shorter than 20 us measure launch latency, not the SM: leave the table alone.
-    if (sm < kMaxSms && dt > 20000) {
-      const float speed = static_cast<float>(cols_done) * T / static_cast<float>(dt);
-      // Running mean over the first 1 / smoothing measurements, exponential
-      // after: one tile's time is noisy (+-2 % from call to call on the same
-      // addresses), and noise in the table is imbalance in the next call.
-      const unsigned int n = g_sm_samples[sm] + 1u;
-      const float weight = fmaxf(args.smoothing, 1.0f / static_cast<float>(n));
-      const float old = g_sm_speed[sm];
-      g_sm_speed[sm] = old > 0.0f ? old + weight * (speed - old) : speed;
-      if (n < 1000000u) g_sm_samples[sm] = n;
-    }
-  }
 }
 
 

@@ -120,6 +120,15 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
+// ---- programmatic dependent launch --------------------------------------------
+// wait: returns once the kernel before this one in the stream has completed
+// and its memory is visible (at once if this launch was not made dependent).
+// launch_dependents: lets the next, dependent launch place its CTAs on free SMs.
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ---- cp.async (LDGSTS), 4 bytes, any 4-byte alignment ----------------------
 __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");

@@ -102,6 +102,41 @@ static void record_plan(const char* fmt, ...) {
   ++g_plan.kernels;
 }
 
+// Launch configuration of the fused kernels.  Every one of them is launched
+// with programmatic stream serialization: its CTAs may be placed on SMs while
+// the previous kernel of the stream is still draining and do their set-up
+// there; they touch no tensor before griddepcontrol.wait, which returns when
+// that kernel has completed and its writes are visible.  Stream order as the
+// caller sees it is unchanged; the launch latency between two kernels is
+// hidden.  VTR_NO_PDL=1 launches them the plain way.
+struct LaunchConfig {
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+};
+static void launch_config(LaunchConfig& l, dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                          int cluster_x = 0) {
+  static const bool no_pdl = getenv("VTR_NO_PDL") != nullptr;
+  l.cfg = cudaLaunchConfig_t{};
+  l.cfg.gridDim = grid, l.cfg.blockDim = block;
+  l.cfg.dynamicSmemBytes = smem;
+  l.cfg.stream = stream;
+  l.cfg.attrs = l.attr;
+  unsigned int n = 0;
+  if (cluster_x > 0) {
+    l.attr[n].id = cudaLaunchAttributeClusterDimension;
+    l.attr[n].val.clusterDim.x = cluster_x;
+    l.attr[n].val.clusterDim.y = 1;
+    l.attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (!no_pdl) {
+    l.attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    l.attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  l.cfg.numAttrs = n;
+}
+
 template <int A_CT, bool GRADS>
 static int launch_tiles(const TileArgs& args, int tiles, int warps, size_t smem, cudaStream_t stream) {
   if (g_plan.dry_run) {
@@ -114,8 +149,9 @@ static int launch_tiles(const TileArgs& args, int tiles, int warps, size_t smem,
   }
   auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
   if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
-  kernel<<<tiles, 32 * warps, smem, stream>>>(args);
-  VTR_CUDA_CHECK(cudaGetLastError());
+  LaunchConfig l;
+  launch_config(l, dim3(tiles), dim3(32 * warps), smem, stream);
+  VTR_CUDA_CHECK(cudaLaunchKernelEx(&l.cfg, kernel, args));
   return VTR_OK;
 }
 
@@ -203,8 +239,9 @@ static int launch_sm_tile(const SmTileArgs& args, int grid, size_t smem, cudaStr
   }
   auto kernel = fused_sm_tile_kernel<A_CT, GRADS>;
   if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
-  kernel<<<grid, 32 * (args.groups * args.relay + 1), smem, stream>>>(args);
-  VTR_CUDA_CHECK(cudaGetLastError());
+  LaunchConfig l;
+  launch_config(l, dim3(grid), dim3(32 * (args.groups * args.relay + 1)), smem, stream);
+  VTR_CUDA_CHECK(cudaLaunchKernelEx(&l.cfg, kernel, args));
   return VTR_OK;
 }
 
@@ -486,18 +523,9 @@ static int launch_chunk(const ChunkArgs& args, int groups, size_t smem, cudaStre
     if (dev < 0 || dev >= 64 || allowed[dev] < 0)
       return fail(VTR_ERR_UNSUPPORTED, "chunk kernel: clusters of %d CTAs are not available", args.chunks);
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(args.chunks, groups, 1);
-  cfg.blockDim = dim3(32 * args.steps, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = args.chunks;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  LaunchConfig l;
+  launch_config(l, dim3(args.chunks, groups, 1), dim3(32 * args.steps), smem, stream, args.chunks);
+  cudaLaunchConfig_t& cfg = l.cfg;
   if (args.chunks > 8) {
     int clusters = 0;
     if (cudaOccupancyMaxActiveClusters(&clusters, kernel, &cfg) != cudaSuccess || clusters < 1) {
@@ -595,8 +623,9 @@ static int launch_item(const ItemArgs& args, cudaStream_t stream) {
                                       : "");
     return VTR_OK;
   }
-  fused_item_kernel<A_CT, GRADS><<<args.f.B, threads, 0, stream>>>(args);
-  VTR_CUDA_CHECK(cudaGetLastError());
+  LaunchConfig l;
+  launch_config(l, dim3(args.f.B), dim3(threads), 0, stream);
+  VTR_CUDA_CHECK(cudaLaunchKernelEx(&l.cfg, fused_item_kernel<A_CT, GRADS>, args));
   return VTR_OK;
 }
 
