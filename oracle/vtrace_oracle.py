@@ -19,15 +19,30 @@ plus the closed-form gradients of that total loss w.r.t. the target logits and
 the baseline values (what ``optimizer.minimize`` at ``experiment.py:415``
 back-propagates into the network heads).
 
-Pinning.  V-trace itself (``from_importance_weights``, the action log-probs
-and ``from_logits``) is pinned against the reference's own numpy ground truth
-``_ground_truth_calculation`` (``vtrace_test.py:44-83``), lifted from the
-reference sources by ``oracle/lift_reference.py`` and frozen as fixtures under
-``tests/golden/`` (see ``tests/golden/make_golden.py``).  The three loss
-helpers, the reward clipping and every gradient are **parity unpinned**: the
-reference holds no test, golden vector or fixture for them and TensorFlow 1.x
-cannot be installed here, so for those rows this restatement (cross-checked
-against torch float64 autograd in ``tests/test_oracle.py``) is the oracle.
+Pinning.  Two independent sources, both the reference's own code, frozen as
+fixtures under ``tests/golden/``:
+
+1. V-trace (``from_importance_weights``, the action log-probs, ``from_logits``)
+   against the reference's numpy ground truth ``_ground_truth_calculation``
+   (``vtrace_test.py:44-83``), lifted by ``oracle/lift_reference.lift`` ->
+   ``vtrace_golden.npz`` (``tests/golden/make_golden.py``).
+2. Everything - V-trace as ``vtrace.py`` itself writes it, the three loss
+   helpers (``experiment.py:324-343``), bootstrap value, T+1 -> T shifts,
+   reward clipping, discounts and the weighted total (``:366-407``), and the
+   gradients into the policy logits and the baseline - against the
+   reference's TensorFlow source EXECUTED over ``oracle/tf_shim.py``, a
+   stand-in for the ~20 elementary TF names that code uses, on torch float64
+   with autograd (``oracle/lift_reference.lift_tf_path`` ->
+   ``losses_golden.npz``, ``tests/golden/make_golden_losses.py``).  The
+   generator checks the stand-in itself: the TF code run over it reproduces
+   source 1 to 1e-12.  ``tests/test_reference_pin.py`` holds this oracle to
+   those fixtures at 1e-12.
+
+What stays restated rather than executed: the TF primitives behind the
+stand-in (``reduce_sum``, ``softmax``, ``sparse_softmax_cross_entropy`` ...),
+one line each from the TF 1.x API documentation, because TensorFlow 1.x cannot
+be installed here.  RMSProp (``oracle/rmsprop_oracle.py``) is TF library code
+that is not in the reference tree: **parity unpinned**.
 """
 import collections
 

@@ -4,8 +4,9 @@
   (tests/golden/, produced by code lifted from vtrace_test.py);
 * against the hard-coded known-answer values of vtrace_test.py:120-156;
 * against the live lifted ground truth when /root/reference is mounted;
-* loss helpers / gradients (unpinned in the reference) against torch float64
-  autograd of an independent restatement.
+* loss helpers / gradients against torch float64 autograd of an independent
+  restatement (tests/test_reference_pin.py pins them to the reference's own
+  TensorFlow source, executed over oracle/tf_shim.py).
 """
 import numpy as np
 import pytest
