@@ -294,15 +294,13 @@ __global__ void __launch_bounds__(32 * kChunkMaxSteps, (A_CT > 0 && A_CT <= 9) ?
     const double ent_sum = warp_sum_fixed(sums.entropy);
     if (lane == 0) sh_sums[3 * warp] = pg_sum, sh_sums[3 * warp + 1] = bl_sum, sh_sums[3 * warp + 2] = ent_sum;
     __syncthreads();
-    if (warp == 0) {
-      if (lane == 0) {
-        double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-        for (int k = 0; k < n; ++k) p0 += sh_sums[3 * k], p1 += sh_sums[3 * k + 1], p2 += sh_sums[3 * k + 2];
-        double* out = a.partials + 3 * (static_cast<size_t>(blockIdx.y) * C + c);
-        out[0] = p0, out[1] = p1, out[2] = p2;
-      }
-      if (args.fin.ticket) finish_losses(a, args.fin);
+    if (threadIdx.x == 0) {
+      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+      for (int k = 0; k < n; ++k) p0 += sh_sums[3 * k], p1 += sh_sums[3 * k + 1], p2 += sh_sums[3 * k + 2];
+      double* out = a.partials + 3 * (static_cast<size_t>(blockIdx.y) * C + c);
+      out[0] = p0, out[1] = p1, out[2] = p2;
     }
+    if (args.fin.ticket) finish_losses_cta(a, args.fin, sh_sums);
   }
   // the bulk store must have read its staging row before the CTA goes away
   if (GRADS && tma_out && has_step && lane == 0) ptx::bulk_wait_read<0>();

@@ -31,6 +31,34 @@ struct TileArgs {
   FinishArgs fin;  // ticket == null: the host appends K3
 };
 
+// The end of both variants below: one warp holds the three sums of the whole
+// batch (every lane the same values) and forms the total, does the peer
+// exchange and writes the results.
+__device__ __forceinline__ void finish_publish(const FusedArgs& a, const FinishArgs& fin, double pg, double bl,
+                                               double ent) {
+  const int lane = threadIdx.x & 31;
+  const double total =
+      pg + static_cast<double>(a.baseline_cost) * bl + static_cast<double>(a.entropy_cost) * ent;
+  if (lane < fin.ex_world)  // lane r stores this rank's four scalars into peer r
+    exchange_publish4_to_peer(fin.ex_peers.p[lane], static_cast<float>(pg), static_cast<float>(bl),
+                              static_cast<float>(ent), static_cast<float>(total), fin.ex_rank,
+                              fin.ex_world, fin.ex_seq);
+  if (fin.ex_world > 0 && fin.ex_sums && fin.ex_seq > fin.ex_lag) {
+    __syncwarp();
+    exchange_collect_warp(fin.ex_peers.p[fin.ex_rank], 4, fin.ex_world, fin.ex_seq - fin.ex_lag,
+                          fin.ex_sums, kExchangeTimeoutNs);
+  }
+  if (lane == 0) {
+    if (fin.losses) {
+      fin.losses[0] = static_cast<float>(pg), fin.losses[1] = static_cast<float>(bl);
+      fin.losses[2] = static_cast<float>(ent), fin.losses[3] = static_cast<float>(total);
+    }
+    if (fin.losses_f64)
+      fin.losses_f64[0] = pg, fin.losses_f64[1] = bl, fin.losses_f64[2] = ent, fin.losses_f64[3] = total;
+    if (a.total_out) *a.total_out = static_cast<float>(total);
+  }
+}
+
 // Called by ONE whole warp of every CTA, after its lane 0 has written the
 // CTA's partial(s).  The summation order depends on the launch shape only:
 // partials strided over the 32 lanes, then a fixed tree.
@@ -63,26 +91,52 @@ __device__ __forceinline__ void finish_losses(const FusedArgs& a, const FinishAr
     for (int u = 0; u < 4; ++u) pg += v[u][0], bl += v[u][1], ent += v[u][2];
   }
   pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
-  const double total =
-      pg + static_cast<double>(a.baseline_cost) * bl + static_cast<double>(a.entropy_cost) * ent;
-  if (lane < fin.ex_world)  // lane r stores this rank's four scalars into peer r
-    exchange_publish4_to_peer(fin.ex_peers.p[lane], static_cast<float>(pg), static_cast<float>(bl),
-                              static_cast<float>(ent), static_cast<float>(total), fin.ex_rank,
-                              fin.ex_world, fin.ex_seq);
-  if (fin.ex_world > 0 && fin.ex_sums && fin.ex_seq > fin.ex_lag) {
-    __syncwarp();
-    exchange_collect_warp(fin.ex_peers.p[fin.ex_rank], 4, fin.ex_world, fin.ex_seq - fin.ex_lag,
-                          fin.ex_sums, kExchangeTimeoutNs);
+  finish_publish(a, fin, pg, bl, ent);
+}
+
+// The same stage for kernels whose CTAs have several warps: called by EVERY
+// thread of every CTA (blockDim.x a multiple of 32), after thread 0 has
+// written the CTA's partial(s).  The CTA that finishes last reads the partials
+// with all of its threads - one L2 round trip instead of one per 128 partials
+// - and sums them in an order that depends on the launch shape only: partials
+// strided over the threads, a fixed tree inside each warp, the warps in a
+// fixed tree.  `scratch`: 3 doubles of shared memory per warp, free by now.
+__device__ __forceinline__ void finish_losses_cta(const FusedArgs& a, const FinishArgs& fin, double* scratch) {
+  __shared__ int sh_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int threads = blockDim.x;
+  if (threadIdx.x == 0) {
+    __threadfence();  // this CTA's partial is visible before its ticket is
+    const unsigned int before = atomicAdd(fin.ticket, 1u);
+    const int last = before == static_cast<unsigned int>(fin.num_ctas - 1);
+    if (last) *fin.ticket = 0u;  // everybody has drawn: ready for the next launch
+    sh_last = last;
   }
-  if (lane == 0) {
-    if (fin.losses) {
-      fin.losses[0] = static_cast<float>(pg), fin.losses[1] = static_cast<float>(bl);
-      fin.losses[2] = static_cast<float>(ent), fin.losses[3] = static_cast<float>(total);
+  __syncthreads();
+  if (!sh_last) return;
+  __threadfence();
+  double pg = 0.0, bl = 0.0, ent = 0.0;
+  for (int i0 = threadIdx.x; i0 < fin.num_partials; i0 += 2 * threads) {
+    double v[2][3];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int i = i0 + threads * u;
+      const bool in = i < fin.num_partials;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) v[u][k] = in ? __ldcg(a.partials + 3 * i + k) : 0.0;
     }
-    if (fin.losses_f64)
-      fin.losses_f64[0] = pg, fin.losses_f64[1] = bl, fin.losses_f64[2] = ent, fin.losses_f64[3] = total;
-    if (a.total_out) *a.total_out = static_cast<float>(total);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) pg += v[u][0], bl += v[u][1], ent += v[u][2];
   }
+  pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
+  if (lane == 0) scratch[3 * warp] = pg, scratch[3 * warp + 1] = bl, scratch[3 * warp + 2] = ent;
+  __syncthreads();
+  if (warp != 0) return;
+  const bool has = lane < (threads >> 5);
+  pg = has ? scratch[3 * lane] : 0.0, bl = has ? scratch[3 * lane + 1] : 0.0;
+  ent = has ? scratch[3 * lane + 2] : 0.0;
+  pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
+  finish_publish(a, fin, pg, bl, ent);
 }
 
 }  // namespace vtr

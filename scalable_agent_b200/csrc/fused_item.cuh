@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kItemMaxSteps) fused_item_kernel(const __grid_
       double* out = a.partials + 3 * static_cast<size_t>(b);
       out[0] = p0, out[1] = p1, out[2] = p2;
     }
-    if (args.fin.ticket && warp == 0) finish_losses(a, args.fin);
+    if (args.fin.ticket) finish_losses_cta(a, args.fin, sh_sums);
   }
 }
 

@@ -218,16 +218,14 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
     if (lane == 0)
       warp_sums[3 * warp] = pg_sum, warp_sums[3 * warp + 1] = bl_sum, warp_sums[3 * warp + 2] = ent_sum;
     __syncthreads();
-    if (warp == 0) {
-      if (lane == 0) {
-        double p0 = 0.0, p1 = 0.0, p2 = 0.0;
-        for (int w = 0; w < W; ++w)
-          p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
-        double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
-        out[0] = p0, out[1] = p1, out[2] = p2;
-      }
-      if (args.fin.ticket) finish_losses(a, args.fin);
+    if (threadIdx.x == 0) {
+      double p0 = 0.0, p1 = 0.0, p2 = 0.0;
+      for (int w = 0; w < W; ++w)
+        p0 += warp_sums[3 * w], p1 += warp_sums[3 * w + 1], p2 += warp_sums[3 * w + 2];
+      double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
+      out[0] = p0, out[1] = p1, out[2] = p2;
     }
+    if (args.fin.ticket) finish_losses_cta(a, args.fin, warp_sums);
   }
   // the bulk stores must have read their staging rows before the CTA goes away
   if (GRADS && tma_out && lane == 0) ptx::bulk_wait_read<0>();
