@@ -305,17 +305,20 @@ int vtr_baseline_loss_bwd_f32(const float* advantages, const float* grad_out,
  * torch symmetric memory); `peer_buffers` is a HOST array of the `world`
  * device pointers to those buffers as mapped on this rank, its own included.
  * Per step, with `seq` = 1, 2, 3, ... identical on all ranks:
- *   vtr_exchange_publish_f32: stores values[0..n) and then seq into slot
- *     [seq % 4][rank] of every peer's buffer (n <= 6);
- *   vtr_exchange_collect_f32: waits (at most 2 s, then writes NaN) until all
- *     `world` slots of step seq in this rank's buffer carry seq, and writes
- *     their sum, accumulated in double in rank order, to sums[0..n).
+ *   vtr_exchange_publish_f32: stores values[0..n), each as one 8-byte word
+ *     {value, seq}, into slot [seq % 4][rank] of every peer's buffer (n <= 6);
+ *     a word says for itself which step it belongs to, so there is no flag
+ *     and no fence between values and flag;
+ *   vtr_exchange_collect_f32: waits (at most 2 s, then writes NaN) until the
+ *     n words of all `world` slots of step seq in this rank's buffer carry
+ *     seq, and writes the sums of their values, accumulated in double in rank
+ *     order, to sums[0..n).
  * A slot is reused four steps later: a rank must have collected step seq - 2
  * (itself or through exchange_sums) before it publishes step seq; it may
  * publish one step without collecting the one before (exchange_lag = 1).
  */
 #define VTR_EXCHANGE_MAX_RANKS 16
-#define VTR_EXCHANGE_SLOT_FLOATS 8
+#define VTR_EXCHANGE_SLOT_FLOATS 16
 #define VTR_EXCHANGE_SLOTS 4
 size_t vtr_exchange_buffer_bytes(int32_t world);
 int vtr_exchange_publish_f32(const float* values, int32_t n, void* const* peer_buffers, int32_t rank,

@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   // after it and owns whatever is left - up to a full tile in this pass, the
   // rest in further passes of the loop below.  Too much handed out is harmless:
   // late tiles find the cursor at B and leave.
-  __shared__ int sh_range[3];  // first column, columns, drew the last ticket
+  __shared__ int sh_range[4];  // first column, columns, drew the last ticket, drew the first ticket
   const int total_gran = B >> 2;
   if (args.cursor) {
     if (warp == 0) {
@@ -172,6 +172,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
         sh_range[0] = static_cast<int>(min(start, static_cast<unsigned int>(B)));
         sh_range[1] = max(0, min(last ? cols : share * 4, B - sh_range[0]));
         sh_range[2] = last;
+        sh_range[3] = static_cast<unsigned int>(drawn >> 32) == 0u;
       }
     }
   } else if (threadIdx.x == 0) {
@@ -179,7 +180,7 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
     const int base = total_gran / G, rem = total_gran % G;
     sh_range[0] = (c * base + min(c, rem)) * 4;
     sh_range[1] = (base + (c < rem ? 1 : 0)) * 4;
-    sh_range[2] = 0;
+    sh_range[2] = 0, sh_range[3] = 0;
   }
 
   const int slot_floats = cols * (2 * A + 4);
@@ -198,6 +199,18 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
   // The SM's speed is measured from here: time spent waiting for the previous
   // kernel says nothing about this SM.
   const unsigned long long t_begin = global_timer_ns();
+
+  // Sharded batch with exchange_lag > 0: the sums wanted are those of an
+  // earlier step, which do not depend on this launch.  The first tile to start
+  // fetches them now (normally they are already in this rank's buffer), next
+  // to the streaming instead of behind it at the end of the launch.
+  if (warp == 0 && args.cursor && args.ex_world > 0 && args.ex_sums && args.ex_lag > 0 &&
+      args.ex_seq > args.ex_lag) {
+    __syncwarp();
+    if (sh_range[3])
+      exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world, args.ex_seq - args.ex_lag,
+                            args.ex_sums, kExchangeTimeoutNs);
+  }
 
   for (int pass = 0;; ++pass) {  // one pass, except for the last ticket's leftovers
   if (threadIdx.x == 0) {
@@ -492,10 +505,10 @@ __global__ void __launch_bounds__(32 * (kSmMaxConsumerWarps + 1), 1)
                                         static_cast<float>(ent), static_cast<float>(total), args.ex_rank,
                                         args.ex_world, args.ex_seq);
             }
-            if (args.ex_world > 0 && args.ex_sums && args.ex_seq > args.ex_lag) {
+            if (args.ex_world > 0 && args.ex_sums && args.ex_lag == 0) {
               __syncwarp();
-              exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world,
-                                    args.ex_seq - args.ex_lag, args.ex_sums, kExchangeTimeoutNs);
+              exchange_collect_warp(args.ex_peers.p[args.ex_rank], 4, args.ex_world, args.ex_seq,
+                                    args.ex_sums, kExchangeTimeoutNs);
             }
             if (lane == 0) {
               if (a.losses) {
