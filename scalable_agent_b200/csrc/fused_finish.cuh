@@ -34,8 +34,10 @@ struct TileArgs {
 // The end of both variants below: one warp holds the three sums of the whole
 // batch (every lane the same values) and forms the total, does the peer
 // exchange and writes the results.
+// `lagged_done`: the sums of step ex_seq - ex_lag (ex_lag > 0) were already
+// fetched earlier in this launch (collect_lagged_early).
 __device__ __forceinline__ void finish_publish(const FusedArgs& a, const FinishArgs& fin, double pg, double bl,
-                                               double ent) {
+                                               double ent, bool lagged_done = false) {
   const int lane = threadIdx.x & 31;
   const double total =
       pg + static_cast<double>(a.baseline_cost) * bl + static_cast<double>(a.entropy_cost) * ent;
@@ -43,7 +45,7 @@ __device__ __forceinline__ void finish_publish(const FusedArgs& a, const FinishA
     exchange_publish4_to_peer(fin.ex_peers.p[lane], static_cast<float>(pg), static_cast<float>(bl),
                               static_cast<float>(ent), static_cast<float>(total), fin.ex_rank,
                               fin.ex_world, fin.ex_seq);
-  if (fin.ex_world > 0 && fin.ex_sums && fin.ex_seq > fin.ex_lag) {
+  if (fin.ex_world > 0 && fin.ex_sums && fin.ex_seq > fin.ex_lag && !(lagged_done && fin.ex_lag > 0)) {
     __syncwarp();
     exchange_collect_warp(fin.ex_peers.p[fin.ex_rank], 4, fin.ex_world, fin.ex_seq - fin.ex_lag,
                           fin.ex_sums, kExchangeTimeoutNs);
@@ -57,6 +59,17 @@ __device__ __forceinline__ void finish_publish(const FusedArgs& a, const FinishA
       fin.losses_f64[0] = pg, fin.losses_f64[1] = bl, fin.losses_f64[2] = ent, fin.losses_f64[3] = total;
     if (a.total_out) *a.total_out = static_cast<float>(total);
   }
+}
+
+// Sharded batch with exchange_lag > 0: the sums wanted are those of an earlier
+// step and do not depend on this launch, so one warp with time to spare can
+// fetch them while the launch streams (normally they are already in this
+// rank's buffer) instead of the last CTA doing it behind everything else.
+// Called by one whole warp of ONE CTA.
+__device__ __forceinline__ void collect_lagged_early(const FinishArgs& fin) {
+  if (fin.ticket && fin.ex_world > 0 && fin.ex_sums && fin.ex_lag > 0 && fin.ex_seq > fin.ex_lag)
+    exchange_collect_warp(fin.ex_peers.p[fin.ex_rank], 4, fin.ex_world, fin.ex_seq - fin.ex_lag, fin.ex_sums,
+                          kExchangeTimeoutNs);
 }
 
 // Called by ONE whole warp of every CTA, after its lane 0 has written the
@@ -101,7 +114,8 @@ __device__ __forceinline__ void finish_losses(const FusedArgs& a, const FinishAr
 // - and sums them in an order that depends on the launch shape only: partials
 // strided over the threads, a fixed tree inside each warp, the warps in a
 // fixed tree.  `scratch`: 3 doubles of shared memory per warp, free by now.
-__device__ __forceinline__ void finish_losses_cta(const FusedArgs& a, const FinishArgs& fin, double* scratch) {
+__device__ __forceinline__ void finish_losses_cta(const FusedArgs& a, const FinishArgs& fin, double* scratch,
+                                                  bool lagged_done = false) {
   __shared__ int sh_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int threads = blockDim.x;
@@ -136,7 +150,7 @@ __device__ __forceinline__ void finish_losses_cta(const FusedArgs& a, const Fini
   pg = has ? scratch[3 * lane] : 0.0, bl = has ? scratch[3 * lane + 1] : 0.0;
   ent = has ? scratch[3 * lane + 2] : 0.0;
   pg = warp_sum_fixed(pg), bl = warp_sum_fixed(bl), ent = warp_sum_fixed(ent);
-  finish_publish(a, fin, pg, bl, ent);
+  finish_publish(a, fin, pg, bl, ent, lagged_done);
 }
 
 }  // namespace vtr

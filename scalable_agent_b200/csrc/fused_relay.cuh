@@ -76,6 +76,8 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
   };
   // Step `it` lives in ring slot it % depth and is loaded by the warp that owns it.
   for (int it = warp; it < min(depth, T); it += W) issue(T - 1 - it, it);
+  // The last warp of the relay has W-1 hops to wait for its first carry.
+  if (blockIdx.x == 0 && warp == W - 1) collect_lagged_early(args.fin);
 
   math::LossSums sums = {0.0, 0.0, 0.0};
 
@@ -225,7 +227,7 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       double* out = a.partials + 3 * static_cast<size_t>(blockIdx.x);
       out[0] = p0, out[1] = p1, out[2] = p2;
     }
-    if (args.fin.ticket) finish_losses_cta(a, args.fin, warp_sums);
+    if (args.fin.ticket) finish_losses_cta(a, args.fin, warp_sums, true);
   }
   // the bulk stores must have read their staging rows before the CTA goes away
   if (GRADS && tma_out && lane == 0) ptx::bulk_wait_read<0>();
