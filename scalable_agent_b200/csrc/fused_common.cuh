@@ -43,9 +43,11 @@ struct FusedArgs {
 
 constexpr int kColumnsPerTile = 32;
 constexpr int kColumnBarrierBytes = 128;  // K1a: up to 16 "slot full" mbarriers
-constexpr int kRelayBarrierBytes = 256;   // K1b: 16 "slot full" + 16 "carry arrived"
-constexpr int kMaxDepth = 16;
+constexpr int kRelayBarrierBytes = 512;   // K1b: 32 "slot full" + 32 "carry arrived"
+constexpr int kMaxDepth = 16;             // K1a, K1c
 constexpr int kMaxWarps = 16;
+constexpr int kRelayMaxDepth = 32;
+constexpr int kRelayMaxWarps = 16;        // K1b: a tile is issue-bound from ~16 warps on (20 and 24 measured the same)
 
 template <int N>
 __device__ __forceinline__ void load_row(float (&x)[N], const float* row) {

@@ -27,6 +27,8 @@ namespace vtr {
 // at 80 registers, so that 24 warps fit an SM's register file.
 // ---------------------------------------------------------------------------
 template <int A_CT, bool GRADS>
+// 768 threads per SM is what the host makes resident (24 warps: one tile of 16,
+// two of 12, three of 8 ...), so the register budget is that of 768 threads.
 __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ TileArgs args) {
   const FusedArgs& a = args.f;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
   float* carry_buf = staging + (GRADS ? W * 32 * A : 0);
   double* warp_sums = reinterpret_cast<double*>(carry_buf + W * 96);
   const uint32_t full_bars = ptx::smem_u32(smem_raw);
-  const uint32_t carry_bars = full_bars + 128u;
+  const uint32_t carry_bars = full_bars + 256u;
   const uint32_t ring_u32 = ptx::smem_u32(ring);
   const uint32_t row_bytes = static_cast<uint32_t>(nb) * A * 4u;
   const int row_elems = nb * A;
@@ -81,13 +83,18 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
 
   math::LossSums sums = {0.0, 0.0, 0.0};
 
-  for (int it = warp; it < T; it += W) {
+  // Running forms of it % depth, (it / depth) & 1 and it / W: no division in the loop.
+  // W < depth whenever the ring wraps (the host sees to it), so one
+  // conditional subtraction keeps the slot index in range.
+  int s = warp % depth;
+  uint32_t full_parity = (warp / depth) & 1;
+  int my_steps = 0;  // steps this warp has done = it / W
+  for (int it = warp; it < T; it += W, ++my_steps) {
     const int t = T - 1 - it;
     const size_t e = static_cast<size_t>(t) * B + b;
-    const int s = it % depth;
     const uint8_t done_cur = (a.done && active) ? a.done[e] : 0;
 
-    ptx::mbar_wait(full_bars + 8u * s, (it / depth) & 1);
+    ptx::mbar_wait(full_bars + 8u * s, full_parity);
     const float* slot = ring + static_cast<size_t>(s) * slot_floats;
     const float* xb_row = slot + lane * A;
     const float* xt_row = slot + 32 * A + lane * A;
@@ -122,7 +129,9 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
     float t_lp = 0.0f, b_lp = 0.0f, log_rho = 0.0f;
     float entropy = 0.0f, inv_sum = 0.0f;
     math::Weights w = {0.0f, 0.0f, 0.0f};
+    float v_next = 0.0f;  // V(x_{t+1}): input data, not part of the recurrence (vtrace.py:243-244)
     if (active) {
+      v_next = it == 0 ? a.bootstrap[b] : __ldg(a.values + e + B);
       rew = math::clip_reward(rew, a.reward_clip_mode);
       // action log-probs of both policies (vtrace.py:143-146)
       if constexpr (A_CT > 0) {
@@ -142,27 +151,26 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       }
     }
 
-    // ---- phase B: the V-trace step (vtrace.py:243-276); needs step t+1 ----
-    math::Carry carry;
-    if (it == 0) {
-      carry.acc = 0.0f;
-      carry.v_next = active ? a.bootstrap[b] : 0.0f;
-      carry.vs_next = carry.v_next;
-    } else {
+    // ---- phase B: the V-trace step (vtrace.py:243-276).  Only acc_{t+1} comes
+    // from the previous warp; everything else of the step is ready. ----
+    const float delta = math::step_delta(w, rew, disc, val, v_next);
+    const float gain = math::step_gain(w, disc);
+    float acc_in = 0.0f;
+    if (it > 0) {
       // n-th use of this warp's carry slot: steps warp, warp+W, ... (step 0 has none)
-      const int use = it / W - (warp == 0 ? 1 : 0);
+      const int use = my_steps - (warp == 0 ? 1 : 0);
       ptx::mbar_wait(carry_bars + 8u * warp, use & 1);
-      const float* cb = carry_buf + warp * 96;
-      carry.acc = cb[lane], carry.v_next = cb[32 + lane], carry.vs_next = cb[64 + lane];
+      acc_in = carry_buf[warp * 32 + lane];
     }
-    float vs, pg;
-    math::vtrace_step(w, rew, disc, val, carry, vs, pg);
+    const float acc = math::step_acc(gain, acc_in, delta);
     if (it + 1 < T) {
       const int nw = warp + 1 == W ? 0 : warp + 1;  // owner of step it+1
-      float* cb = carry_buf + nw * 96;
-      cb[lane] = carry.acc, cb[32 + lane] = carry.v_next, cb[64 + lane] = carry.vs_next;
+      carry_buf[nw * 32 + lane] = acc;
       ptx::mbar_arrive(carry_bars + 8u * nw);
     }
+    const float vs = __fadd_rn(acc, val);  // vtrace.py:265
+    // vs_{t+1} = acc_{t+1} + V(x_{t+1}), formed as the previous step formed it
+    const float pg = math::step_pg(w, rew, disc, val, it == 0 ? v_next : __fadd_rn(acc_in, v_next));
 
     // ---- phase C: outputs, gradient row, loss terms ----
     if (GRADS) {
@@ -211,6 +219,8 @@ __global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant_
       __syncwarp();
       if (it + depth < T) issue(t - depth, s);
     }
+    s += W;
+    if (s >= depth) s -= depth, full_parity ^= 1u;
   }
 
   if (a.partials) {

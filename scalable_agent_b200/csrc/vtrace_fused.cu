@@ -699,7 +699,7 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   // the ring still runs at least 2 slots ahead of the warps.
   int warps = resident >= 7 ? 1 : 24 / resident;
   if (const int forced = env_int("VTR_COLUMN_WARPS")) warps = forced;
-  if (warps > kMaxWarps) warps = kMaxWarps;
+  if (warps > kRelayMaxWarps) warps = kRelayMaxWarps;
   if (warps > p->T) warps = p->T;
   if (warps < 1) warps = 1;
   long depth = 0;
@@ -709,7 +709,7 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
     if (warps == 1 || depth >= warps + 2) break;
   }
   if (const int forced = env_int("VTR_COLUMN_DEPTH")) depth = forced;
-  if (depth > kMaxDepth) depth = kMaxDepth;
+  if (depth > (warps > 1 ? kRelayMaxDepth : kMaxDepth)) depth = warps > 1 ? kRelayMaxDepth : kMaxDepth;
   if (depth > p->T) depth = p->T;
   if (depth < 2) depth = p->T < 2 ? 1 : 2;
   // Waiting on a slot by parity needs the slot's previous use to be complete;
