@@ -34,16 +34,21 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
+// Without a hint try_wait comes back after a few tens of cycles and the caller
+// spins (measured in K1b: ~15 failed tries, ~75 issued instructions, per warp
+// and step, in a kernel that is bound by instruction issue).  With one the
+// warp may stay suspended until the phase completes.
+constexpr uint32_t kMbarSuspendNs = 10000000u;
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
       "selp.u32 %0, 1, 0, p;\n"
       "}\n"
       : "=r"(ok)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(kMbarSuspendNs)
       : "memory");
   return ok != 0;
 }

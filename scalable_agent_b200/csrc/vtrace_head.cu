@@ -102,14 +102,14 @@ static size_t smem_bytes(int K) {
 
 // ---- PTX ---------------------------------------------------------------------
 __device__ __forceinline__ void wait_or_trap(uint32_t bar, uint32_t parity) {
+  // A failed try has been suspended for up to ptx::kMbarSuspendNs already:
+  // failures are rare and looking at the clock on each of them costs nothing.
   unsigned long long t0 = 0;
-  for (uint32_t spins = 0; !ptx::mbar_try_wait(bar, parity); ++spins) {
-    if ((spins & 0x3ffu) == 0x3ffu) {
-      unsigned long long now;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > kWatchdogNs) __trap();
-    }
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > kWatchdogNs) __trap();
   }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
