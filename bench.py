@@ -532,6 +532,50 @@ def run_gpu(args):
       'vs_kernel': api_ms / (total_ms / K),
       'api': 'scalable_agent_b200.experiment.compute_vtrace_loss + backward, '
              'device-resident inputs, CUDA events'}
+
+  # The same step through compute_vtrace_loss_and_grads (no autograd node: the
+  # losses and both gradients straight from the one launch), here and at
+  # BASELINE.json's config 2, where the host side is all there is.
+  def timed(fn, steps):
+    for _ in range(5):
+      fn()
+    torch.cuda.synchronize()
+    b = torch.cuda.Event(enable_timing=True)
+    e = torch.cuda.Event(enable_timing=True)
+    b.record()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+      fn()
+    host = time.perf_counter() - t0
+    e.record()
+    torch.cuda.synchronize()
+    return b.elapsed_time(e) / steps, host / steps * 1e3
+
+  def direct_step(batch):
+    return lambda: experiment.compute_vtrace_loss_and_grads(
+        baseline_cost=BASELINE_COST, entropy_cost=ENTROPY_COST, **batch)
+
+  def autograd_step(batch):
+    def step():
+      batch['target_policy_logits'].grad = None
+      batch['values'].grad = None
+      experiment.compute_vtrace_loss(
+          baseline_cost=BASELINE_COST, entropy_cost=ENTROPY_COST, return_aux=False, **batch).total_loss.backward()
+    return step
+
+  if world == 1:
+    d_ms, d_host = timed(direct_step(api_in), K)
+    api_device['direct'] = {
+        'ms_per_step': d_ms, 'host_ms_per_step': d_host, 'vs_kernel': d_ms / (total_ms / K),
+        'api': 'experiment.compute_vtrace_loss_and_grads (losses + gradients, no autograd node)'}
+    small = synthetic_on_device(100, 32, 9, 2, device)
+    small['target_policy_logits'] = small['target_policy_logits'].detach().requires_grad_(True)
+    small['values'] = small['values'].detach().requires_grad_(True)
+    a_ms, a_host = timed(autograd_step(small), 300)
+    s_ms, s_host = timed(direct_step(small), 300)
+    api_device['config2'] = {
+        'workload': 'T=100 B=32 A=9', 'autograd_ms_per_step': a_ms, 'autograd_host_ms_per_step': a_host,
+        'direct_ms_per_step': s_ms, 'direct_host_ms_per_step': s_host}
   del api_in
 
   # ---- the heads upstream of the path (experiment.py:199-203) ---------------

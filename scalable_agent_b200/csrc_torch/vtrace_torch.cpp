@@ -310,10 +310,59 @@ std::vector<c10::optional<Tensor>> fused_learner_loss(const Tensor& learner_logi
                                                discounting, reward_clip_mode, want_aux, path));
 }
 
+// The same two launches without an autograd node, for a learner that feeds the
+// gradients to the heads' backward itself (torch.autograd.backward([logits,
+// baseline], [d_logits, d_baseline])): the losses and both gradients are
+// results of the one forward launch anyway, and the autograd engine's hop for
+// this node costs more than the kernel at small shapes.
+// Python: (total, losses, vs, pg_advantages, d_target_logits, d_values)
+std::vector<Tensor> fused_loss_and_grads(const Tensor& behaviour, const Tensor& target, const Tensor& actions,
+                                         const c10::optional<Tensor>& discounts, const Tensor& rewards,
+                                         const Tensor& values, const Tensor& bootstrap,
+                                         const c10::optional<Tensor>& done, c10::optional<double> clip_rho,
+                                         c10::optional<double> clip_pg_rho, double baseline_cost,
+                                         double entropy_cost, double discounting, int64_t reward_clip_mode,
+                                         int64_t path) {
+  const Options o = {clip_rho, clip_pg_rho, baseline_cost, entropy_cost, discounting, reward_clip_mode, path,
+                     false, false};
+  std::vector<Tensor> r = launch(behaviour, target, actions, discounts, rewards, values, bootstrap, done, o, true);
+  const int64_t T = target.size(0), B = target.size(1), A = target.size(2);
+  const Tensor grads = r.back();
+  return {r[0], r[1], r[2], r[3], d_logits_of(grads, T, B, A), d_values_of(grads, T, B, A)};
+}
+
+// [T+1, ...] tensors as build_learner has them; gradients [T+1, ...] with a zero last step.
+std::vector<Tensor> fused_learner_loss_and_grads(const Tensor& learner_logits, const Tensor& learner_baseline,
+                                                 const Tensor& behaviour_logits, const Tensor& actions,
+                                                 const Tensor& rewards, const Tensor& done,
+                                                 c10::optional<double> clip_rho, c10::optional<double> clip_pg_rho,
+                                                 double baseline_cost, double entropy_cost, double discounting,
+                                                 int64_t reward_clip_mode, int64_t path) {
+  TORCH_CHECK_VALUE(learner_logits.dim() == 3, "learner_policy_logits must have rank 3, got shape ",
+                    learner_logits.sizes());
+  const int64_t T = learner_logits.size(0) - 1, B = learner_logits.size(1), A = learner_logits.size(2);
+  TORCH_CHECK_VALUE(T >= 1, "need at least 2 time steps (T+1), got ", T + 1);
+  for (const Tensor* t : {&learner_baseline, &actions, &rewards, &done})
+    TORCH_CHECK_VALUE(t->dim() == 2 && t->size(0) == T + 1 && t->size(1) == B,
+                      "learner_baseline, actions, rewards and done must have shape [T+1, B]");
+  TORCH_CHECK_VALUE(behaviour_logits.sizes() == learner_logits.sizes(),
+                    "behaviour and learner logits differ in shape");
+  const Options o = {clip_rho, clip_pg_rho, baseline_cost, entropy_cost, discounting, reward_clip_mode, path,
+                     false, true};
+  std::vector<Tensor> r =
+      launch(behaviour_logits.narrow(0, 1, T), learner_logits.narrow(0, 0, T), actions.narrow(0, 1, T),
+             c10::nullopt, rewards.narrow(0, 1, T), learner_baseline.narrow(0, 0, T),
+             learner_baseline.select(0, T), done.narrow(0, 1, T), o, true);
+  const Tensor grads = r.back();
+  return {r[0], r[1], r[2], r[3], d_logits_of(grads, T + 1, B, A), d_values_of(grads, T + 1, B, A)};
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("bind", &bind, "hand over the addresses of the C ABI entry points");
   m.def("fused_loss", &fused_loss);
   m.def("fused_learner_loss", &fused_learner_loss);
+  m.def("fused_loss_and_grads", &fused_loss_and_grads);
+  m.def("fused_learner_loss_and_grads", &fused_learner_loss_and_grads);
 }

@@ -275,3 +275,106 @@ def compute_learner_loss(
       vtrace_returns=vtrace.VTraceFromLogitsReturns(
           vs=vs, pg_advantages=pg, log_rhos=aux[0],
           behaviour_action_log_probs=aux[1], target_action_log_probs=aux[2]))
+
+
+VTraceLossAndGrads = collections.namedtuple(
+    'VTraceLossAndGrads',
+    ['total_loss', 'policy_gradient_loss', 'baseline_loss', 'entropy_loss',
+     'vs', 'pg_advantages', 'd_policy_logits', 'd_baseline'])
+
+
+def _loss_and_grads(total, losses, vs, pg, d_logits, d_baseline):
+  return VTraceLossAndGrads(
+      total_loss=total, policy_gradient_loss=losses[0], baseline_loss=losses[1],
+      entropy_loss=losses[2], vs=vs, pg_advantages=pg,
+      d_policy_logits=d_logits, d_baseline=d_baseline)
+
+
+def compute_vtrace_loss_and_grads(
+    behaviour_policy_logits, target_policy_logits, actions, discounts,
+    rewards, values, bootstrap_value,
+    clip_rho_threshold=1.0, clip_pg_rho_threshold=1.0,
+    baseline_cost=.5, entropy_cost=.00025,
+    reward_clipping=None, done=None, discounting=.99, path='auto'):
+  """`compute_vtrace_loss` + `total_loss.backward()` as one call without an autograd node.
+
+  The fused pass produces the losses and the gradients of the total w.r.t.
+  `target_policy_logits` and `values` in its one launch; here they are handed
+  back directly, for a learner that continues the backward pass itself:
+
+      r = compute_vtrace_loss_and_grads(...)
+      torch.autograd.backward([logits, baseline], [r.d_policy_logits, r.d_baseline])
+
+  which is what `optimizer.minimize(total_loss)` (`experiment.py:415`) does to
+  the heads.  Same kernels and numbers as `compute_vtrace_loss`; the host side
+  is one C++ call (about 10 us against about 60 us through the autograd
+  engine), which is what counts at small shapes.  Nothing returned is
+  differentiable.
+  """
+  ext = None if torch.compiler.is_compiling() else _ext.get()
+  f32 = torch.float32
+  if (ext is not None and reward_clipping in _lib.REWARD_CLIP_MODES and path in _lib.PATHS
+      and _device_ready(
+          (behaviour_policy_logits, f32), (target_policy_logits, f32),
+          (actions, torch.int32), (rewards, f32), (values, f32), (bootstrap_value, f32),
+          (done, torch.bool) if done is not None else (discounts, f32))):
+    return _loss_and_grads(*ext.fused_loss_and_grads(
+        behaviour_policy_logits, target_policy_logits, actions,
+        None if done is not None else discounts, rewards, values, bootstrap_value,
+        done.view(torch.uint8) if done is not None else None,
+        _threshold(clip_rho_threshold, 'clip_rho_threshold'),
+        _threshold(clip_pg_rho_threshold, 'clip_pg_rho_threshold'),
+        float(baseline_cost), float(entropy_cost), float(discounting),
+        _lib.REWARD_CLIP_MODES[reward_clipping], _lib.PATHS[path]))
+  # Anything else (host data, other dtypes, no C++ layer): through the
+  # differentiable call on leaves of our own.
+  dev = _device_of(behaviour_policy_logits, target_policy_logits, actions,
+                   discounts, rewards, values, bootstrap_value)
+  logits = _to(target_policy_logits, f32, dev).detach().clone().requires_grad_(True)
+  baseline = _to(values, f32, dev).detach().clone().requires_grad_(True)
+  out = compute_vtrace_loss(
+      behaviour_policy_logits, logits, actions, discounts, rewards, baseline,
+      bootstrap_value, clip_rho_threshold, clip_pg_rho_threshold, baseline_cost,
+      entropy_cost, reward_clipping, done, discounting, return_aux=False, path=path)
+  out.total_loss.backward()
+  return VTraceLossAndGrads(
+      out.total_loss.detach(), out.policy_gradient_loss, out.baseline_loss, out.entropy_loss,
+      out.vtrace_returns.vs, out.vtrace_returns.pg_advantages, logits.grad, baseline.grad)
+
+
+def compute_learner_loss_and_grads(
+    behaviour_policy_logits, actions, rewards, done,
+    learner_policy_logits, learner_baseline,
+    discounting=.99, reward_clipping='abs_one',
+    baseline_cost=.5, entropy_cost=.00025,
+    clip_rho_threshold=1.0, clip_pg_rho_threshold=1.0, path='auto'):
+  """`compute_learner_loss` + `total_loss.backward()` as one call without an autograd node.
+
+  Arguments as `compute_learner_loss` ([T+1, ...] tensors, `experiment.py:362-407`);
+  `d_policy_logits` and `d_baseline` come back [T+1, ...] with a zero last
+  step.  See `compute_vtrace_loss_and_grads`.
+  """
+  ext = None if torch.compiler.is_compiling() else _ext.get()
+  f32 = torch.float32
+  if (ext is not None and reward_clipping in _lib.REWARD_CLIP_MODES and path in _lib.PATHS
+      and _device_ready(
+          (learner_policy_logits, f32), (learner_baseline, f32), (behaviour_policy_logits, f32),
+          (actions, torch.int32), (rewards, f32), (done, torch.bool))):
+    return _loss_and_grads(*ext.fused_learner_loss_and_grads(
+        learner_policy_logits, learner_baseline, behaviour_policy_logits, actions,
+        rewards, done.view(torch.uint8),
+        _threshold(clip_rho_threshold, 'clip_rho_threshold'),
+        _threshold(clip_pg_rho_threshold, 'clip_pg_rho_threshold'),
+        float(baseline_cost), float(entropy_cost), float(discounting),
+        _lib.REWARD_CLIP_MODES[reward_clipping], _lib.PATHS[path]))
+  dev = _device_of(learner_policy_logits, learner_baseline, behaviour_policy_logits)
+  logits = _to(learner_policy_logits, f32, dev).detach().clone().requires_grad_(True)
+  baseline = _to(learner_baseline, f32, dev).detach().clone().requires_grad_(True)
+  out = compute_learner_loss(
+      behaviour_policy_logits, actions, rewards, done, logits, baseline,
+      discounting, reward_clipping, baseline_cost, entropy_cost,
+      clip_rho_threshold, clip_pg_rho_threshold, return_aux=False, path=path)
+  out.total_loss.backward()
+  return VTraceLossAndGrads(
+      out.total_loss.detach(), out.policy_gradient_loss, out.baseline_loss, out.entropy_loss,
+      out.vtrace_returns.vs, out.vtrace_returns.pg_advantages, logits.grad, baseline.grad)

@@ -627,3 +627,64 @@ def test_done_and_clipping_on_the_item_kernel(api):
   inp['rewards'] = inp['raw_rewards']
   _check_fused(experiment, inp, reward_clipping='abs_one', done_np=inp['done'],
                discounting=0.95, path='item')
+
+
+# ---------------------------------------------------------------------------
+# Losses and gradients without an autograd node
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize('T,B,A,clip', [(5, 2, 3, None), (100, 32, 9, 'abs_one'), (20, 300, 18, 'soft_asymmetric')])
+def test_loss_and_grads_is_the_autograd_path_without_the_node(api, T, B, A, clip):
+  """compute_vtrace_loss_and_grads == compute_vtrace_loss + backward, bit for bit."""
+  _, experiment = api
+  inp = oracle.synthetic_inputs(T, B, A, seed=T + B, reward_clipping=None)
+  kw = dict(reward_clipping=clip, baseline_cost=0.5, entropy_cost=0.01)
+  args, out = _run_fused(experiment, inp, **kw)
+  out.total_loss.backward()
+  plain = {k: _dev(inp[k]) for k in FUSED_KEYS}
+  got = experiment.compute_vtrace_loss_and_grads(**plain, **kw)
+  assert not got.total_loss.requires_grad and got.d_policy_logits.grad_fn is None
+  for a, b in ((got.total_loss, out.total_loss), (got.policy_gradient_loss, out.policy_gradient_loss),
+               (got.baseline_loss, out.baseline_loss), (got.entropy_loss, out.entropy_loss),
+               (got.vs, out.vtrace_returns.vs), (got.pg_advantages, out.vtrace_returns.pg_advantages),
+               (got.d_policy_logits, args['target_policy_logits'].grad), (got.d_baseline, args['values'].grad)):
+    assert torch.equal(a.detach(), b.detach())
+  # and against the oracle
+  ref = oracle.fused_vtrace_loss(*[inp[k] for k in FUSED_KEYS], 1.0, 1.0, 0.5, 0.01, reward_clipping=clip)
+  assert_close(_np(got.total_loss), ref.total_loss, TOL, 'total')
+  assert_close(_np(got.d_policy_logits), ref.d_target_logits, TOL, 'd_logits')
+  assert_close(_np(got.d_baseline), ref.d_values, TOL, 'd_values')
+  # host data takes the generic route to the same numbers
+  host = experiment.compute_vtrace_loss_and_grads(
+      **{k: (inp[k] if k != 'target_policy_logits' else _dev(inp[k])) for k in FUSED_KEYS}, **kw)
+  assert torch.equal(host.d_policy_logits, got.d_policy_logits)
+  assert torch.equal(host.total_loss, got.total_loss)
+
+
+def test_learner_loss_and_grads_feeds_the_heads_backward(api):
+  """The use the call is for: gradients handed to the backward pass of the heads."""
+  _, experiment = api
+  T, B, A, K = 12, 40, 9, 32
+  g = torch.Generator(device='cuda').manual_seed(5)
+  core = torch.randn(T + 1, B, K, generator=g, device='cuda')
+  w = (torch.randn(K, A + 1, generator=g, device='cuda') / K ** 0.5)
+  behaviour = torch.randn(T + 1, B, A, generator=g, device='cuda')
+  actions = torch.randint(0, A, (T + 1, B), generator=g, device='cuda', dtype=torch.int32)
+  rewards = torch.randn(T + 1, B, generator=g, device='cuda')
+  done = torch.rand(T + 1, B, generator=g, device='cuda') < 0.1
+
+  def heads(weight):
+    out = core @ weight
+    return out[..., :A].contiguous(), out[..., A].contiguous()
+
+  w1 = w.clone().requires_grad_(True)
+  logits, baseline = heads(w1)
+  experiment.compute_learner_loss(behaviour, actions, rewards, done, logits, baseline).total_loss.backward()
+
+  w2 = w.clone().requires_grad_(True)
+  logits, baseline = heads(w2)
+  r = experiment.compute_learner_loss_and_grads(behaviour, actions, rewards, done, logits.detach(),
+                                                baseline.detach())
+  assert tuple(r.d_policy_logits.shape) == (T + 1, B, A) and tuple(r.d_baseline.shape) == (T + 1, B)
+  assert float(r.d_policy_logits[-1].abs().max()) == 0.0 and float(r.d_baseline[-1].abs().max()) == 0.0
+  torch.autograd.backward([logits, baseline], [r.d_policy_logits, r.d_baseline])
+  assert torch.equal(w1.grad, w2.grad)
