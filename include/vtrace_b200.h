@@ -45,6 +45,14 @@
  *     update it without synchronisation; the worst that can happen is a less
  *     even partition on the next call.
  *   - The 200 KiB array of vtr_from_logits_fused_noalloc_f32 (see there).
+ *
+ * How the fused pass is launched: with programmatic stream serialization
+ * (cudaLaunchAttributeProgrammaticStreamSerialization).  Its CTAs may be
+ * placed on SMs while the previous kernel of the stream drains and do their
+ * set-up there; they touch no tensor before griddepcontrol.wait, i.e. before
+ * that kernel has completed and its writes are visible.  Stream order as the
+ * caller sees it is the ordinary one.  VTR_NO_PDL=1 in the environment makes
+ * the launches plain ones.
  */
 #ifndef VTRACE_B200_H_
 #define VTRACE_B200_H_
