@@ -19,6 +19,13 @@ from tests.conftest import assert_close
 # experiment.py:92-95
 LR, DECAY, MOMENTUM, EPSILON = 0.00048, 0.99, 0.0, 0.1
 
+TWO_GPU_REASON = (
+    'needs 2 GPUs: two ranks on ONE device would be two processes whose kernels wait for each '
+    "other's stores, which a single GPU may time-slice instead of running side by side (a wait "
+    'could then starve the rank it waits for); bench.py exchange_check / optim_check carry the '
+    'proof on every multi-GPU run')
+
+
 
 # ---------------------------------------------------------------------------
 # CPU: the oracle itself and the host arithmetic of the library
@@ -316,7 +323,7 @@ def test_sharded_optimizer_flags_a_late_peer_on_every_rank(tmp_path):
   half-updated model: both ranks flag the step (device word, pinned host
   word, exception on the next step), and neither slice is half-written."""
   if torch.cuda.device_count() < 2:
-    pytest.skip('needs 2 GPUs')
+    pytest.skip(TWO_GPU_REASON)
   import torch.multiprocessing as mp
   world = 2
   mp.spawn(_late_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
@@ -333,7 +340,7 @@ def test_sharded_optimizer_flags_a_late_peer_on_every_rank(tmp_path):
 @pytest.mark.gpu
 def test_sharded_optimizer_two_ranks(tmp_path):
   if torch.cuda.device_count() < 2:
-    pytest.skip('needs 2 GPUs')
+    pytest.skip(TWO_GPU_REASON)
   import torch.multiprocessing as mp
   world = 2
   mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
