@@ -8,19 +8,21 @@ namespace vtr {
 // ---------------------------------------------------------------------------
 // K1b: several warps per tile, passing the recurrence along ("relay").  Warp w
 // owns the time steps it = w, w+W, ... (it counts from the end: t = T-1-it);
-// each does its whole step in its own registers and only the 3-float carry
-// (acc, V_{t+1}, vs_{t+1}) per lane travels from the owner of step t+1 to the
-// owner of step t, through shared memory and an mbarrier.  Everything that
-// does not depend on the carry (both softmaxes, log_rho, rho, the entropy:
-// most of the work) overlaps between warps, so a tile advances much faster
-// than one warp can; used whenever shared memory leaves room for it.
+// each does its whole step in its own registers and only acc_{t+1}, one float
+// per lane, travels from the owner of step t+1 to the owner of step t, through
+// shared memory and an mbarrier (V_{t+1} is input data and is read ahead of
+// time; vs_{t+1} is re-formed as acc_{t+1} + V_{t+1}).  Everything that does
+// not depend on the carry (both softmaxes, log_rho, rho, the entropy, delta_t
+// and the gain: all but one FMA) overlaps between warps, so a tile advances
+// much faster than one warp can; used whenever shared memory leaves room for
+// it.
 //
 // Shared memory of one tile, in bytes from the start:
-//   [0,128)    `depth` mbarriers "slot full"      (TMA + cp.async completion)
-//   [128,256)  `warps` mbarriers "carry arrived"  (recurrence hand-off)
+//   [0,256)    `depth` mbarriers "slot full"      (TMA + cp.async completion)
+//   [256,512)  `warps` mbarriers "carry arrived"  (recurrence hand-off)
 //   ring       depth slots of slot_floats floats: one time step of the tile each
 //   staging    warps x 32*A floats: each warp's d_target_logits row  (GRADS only)
-//   carry      warps x 3 x 32 floats: (acc, V_{t+1}, vs_{t+1}) per lane
+//   carry      warps x 96 floats, the first 32 used: acc per lane
 //   sums       warps x 3 doubles: per-warp loss partials
 //
 // Launch bound 768 threads (never more than 512 are launched) caps the kernel
