@@ -160,8 +160,19 @@ def from_importance_weights(
 
   # Make sure tensor ranks are consistent (vtrace.py:222-231).
   rho_rank = log_rhos.dim()
-  if rho_rank < 2:
-    raise ValueError('log_rhos must have rank >= 2')
+  if rho_rank == 1:
+    # One sequence without a batch dimension ([T] tensors, scalar bootstrap):
+    # nothing in vtrace.py:222-231 forbids it.  Run it as a batch of one.
+    _assert_rank(values, 1, 'values')
+    _assert_rank(bootstrap_value, 0, 'bootstrap_value')
+    _assert_rank(discounts, 1, 'discounts')
+    _assert_rank(rewards, 1, 'rewards')
+    out = from_importance_weights(
+        log_rhos[:, None], discounts[:, None], rewards[:, None], values[:, None],
+        bootstrap_value[None], clip_rho_threshold, clip_pg_rho_threshold)
+    return VTraceReturns(vs=out.vs[:, 0], pg_advantages=out.pg_advantages[:, 0])
+  if rho_rank < 1:
+    raise ValueError('log_rhos must have rank >= 1')
   _assert_rank(values, rho_rank, 'values')
   _assert_rank(bootstrap_value, rho_rank - 1, 'bootstrap_value')
   _assert_rank(discounts, rho_rank, 'discounts')

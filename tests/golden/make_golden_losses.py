@@ -49,6 +49,9 @@ LEARNER_CASES = [
     ('learner_dmlab30', 100, 4, 18, 'abs_one', 14),
     ('learner_wide', 7, 70, 18, 'soft_asymmetric', 15),
     ('learner_atari', 33, 5, 6, 'abs_one', 16),
+    ('learner_single_step', 1, 1, 2, 'abs_one', 17),           # the smallest batch there is
+    ('learner_one_column', 9, 1, 4, 'soft_asymmetric', 18),
+    ('learner_odd_width', 6, 33, 5, 'abs_one', 19),            # one column past a 32-column tile, A not compiled in
 ]
 
 FROM_LOGITS_CASES = [
@@ -174,6 +177,22 @@ def main():
   for k, v in inp.items():
     out['%s/in/%s' % (name, k)] = v
   got = ref.vtrace.from_importance_weights(**inp)
+  out[name + '/vs'] = _np(got.vs)
+  out[name + '/pg_advantages'] = _np(got.pg_advantages)
+
+  # ... and without a batch dimension: [T] tensors and a scalar bootstrap value
+  rng = np.random.default_rng(32)
+  T = 11
+  inp = dict(
+      log_rhos=rng.standard_normal((T,)).astype(np.float32),
+      discounts=(0.9 * (rng.random((T,)) > 0.1)).astype(np.float32),
+      rewards=rng.standard_normal((T,)).astype(np.float32),
+      values=rng.standard_normal((T,)).astype(np.float32),
+      bootstrap_value=np.float32(rng.standard_normal()))
+  name = 'importance_weights_rank1'
+  for k, v in inp.items():
+    out['%s/in/%s' % (name, k)] = np.asarray(v)
+  got = ref.vtrace.from_importance_weights(clip_rho_threshold=3.7, clip_pg_rho_threshold=2.2, **inp)
   out[name + '/vs'] = _np(got.vs)
   out[name + '/pg_advantages'] = _np(got.pg_advantages)
 

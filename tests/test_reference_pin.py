@@ -20,7 +20,8 @@ LOSSES_PATH = os.path.join(ROOT, 'tests', 'golden', 'losses_golden.npz')
 F64 = 1e-12
 
 LEARNER_CASES = ['learner_config1', 'learner_abs_one', 'learner_soft_asymmetric', 'learner_dmlab30',
-                 'learner_wide', 'learner_atari']
+                 'learner_wide', 'learner_atari', 'learner_single_step', 'learner_one_column',
+                 'learner_odd_width']
 FROM_LOGITS_CASES = ['from_logits_default', 'from_logits_unclipped', 'from_logits_3p7_2p2',
                      'from_logits_rho_only', 'from_logits_long']
 HELPER_CASES = ['helpers_small', 'helpers_dmlab', 'helpers_wide']
@@ -47,7 +48,8 @@ def shifted(c):
 def test_fixture_covers_the_loss_block(losses):
   first, last = (int(x) for x in losses.case('meta')['glue_lines'])
   assert (first, last) == (366, 407)
-  for name in LEARNER_CASES + FROM_LOGITS_CASES + HELPER_CASES + ['importance_weights_trailing']:
+  for name in (LEARNER_CASES + FROM_LOGITS_CASES + HELPER_CASES +
+               ['importance_weights_trailing', 'importance_weights_rank1']):
     assert name in losses.cases, name
 
 
@@ -97,6 +99,15 @@ def test_oracle_importance_weights_with_trailing_dimensions(losses):
                                        c['in/bootstrap_value'])
   assert_close(got.vs, c['vs'], F64, 'vs')
   assert_close(got.pg_advantages, c['pg_advantages'], F64, 'pg_advantages')
+
+
+def test_oracle_importance_weights_without_a_batch_dimension(losses):
+  c = losses.case('importance_weights_rank1')
+  got = oracle.from_importance_weights(
+      c['in/log_rhos'][:, None], c['in/discounts'][:, None], c['in/rewards'][:, None], c['in/values'][:, None],
+      c['in/bootstrap_value'][None], 3.7, 2.2)
+  assert_close(got.vs[:, 0], c['vs'], F64, 'vs')
+  assert_close(got.pg_advantages[:, 0], c['pg_advantages'], F64, 'pg_advantages')
 
 
 @pytest.mark.parametrize('case', HELPER_CASES)

@@ -131,6 +131,17 @@ def test_importance_weights_with_trailing_dimensions_vs_reference_source(api, lo
   assert_close(_np(got.pg_advantages), c['pg_advantages'], TOL, 'pg_advantages')
 
 
+def test_importance_weights_without_a_batch_dimension_vs_reference_source(api, losses):
+  vtrace, _ = api
+  c = losses.case('importance_weights_rank1')
+  got = vtrace.from_importance_weights(
+      _dev(c['in/log_rhos']), _dev(c['in/discounts']), _dev(c['in/rewards']), _dev(c['in/values']),
+      _dev(c['in/bootstrap_value']), clip_rho_threshold=3.7, clip_pg_rho_threshold=2.2)
+  assert tuple(got.vs.shape) == tuple(c['vs'].shape)
+  assert_close(_np(got.vs), c['vs'], TOL, 'vs')
+  assert_close(_np(got.pg_advantages), c['pg_advantages'], TOL, 'pg_advantages')
+
+
 @pytest.mark.parametrize('case', HELPER_CASES)
 def test_loss_helpers_vs_reference_source(api, losses, case):
   """experiment.py:324-343, each helper on its own, values and gradients."""
