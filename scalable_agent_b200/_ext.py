@@ -60,6 +60,7 @@ def get():
         lib = _lib.load()
         module.bind(_addr(lib.vtr_from_logits_fused_f32), _addr(lib.vtr_fused_workspace_bytes),
                     _addr(lib.vtr_scale_inplace_f32), _addr(lib.vtr_last_error))
+        module.bind_importance_weights(_addr(lib.vtr_from_importance_weights_f32))
         ext = module
       except Exception as e:  # pylint: disable=broad-except
         sys.stderr.write('scalable_agent_b200: C++ host layer not usable (%s); '

@@ -35,6 +35,8 @@ struct Abi {
   size_t (*workspace_bytes)(int32_t, int32_t, int32_t) = nullptr;
   int (*scale_inplace)(float*, const float*, int64_t, void*) = nullptr;
   const char* (*last_error)() = nullptr;
+  int (*importance_weights)(const float*, const float*, const float*, const float*, const float*, int32_t, int32_t,
+                            int32_t, uint32_t, float, float, uint32_t, float*, float*, void*) = nullptr;
 } g_abi;
 
 void bind(uintptr_t fused, uintptr_t workspace_bytes, uintptr_t scale_inplace, uintptr_t last_error) {
@@ -42,6 +44,10 @@ void bind(uintptr_t fused, uintptr_t workspace_bytes, uintptr_t scale_inplace, u
   g_abi.workspace_bytes = reinterpret_cast<decltype(g_abi.workspace_bytes)>(workspace_bytes);
   g_abi.scale_inplace = reinterpret_cast<decltype(g_abi.scale_inplace)>(scale_inplace);
   g_abi.last_error = reinterpret_cast<decltype(g_abi.last_error)>(last_error);
+}
+
+void bind_importance_weights(uintptr_t fn) {
+  g_abi.importance_weights = reinterpret_cast<decltype(g_abi.importance_weights)>(fn);
 }
 
 // The C return convention as exceptions: negative = argument error
@@ -357,12 +363,47 @@ std::vector<Tensor> fused_learner_loss_and_grads(const Tensor& learner_logits, c
   return {r[0], r[1], r[2], r[3], d_logits_of(grads, T + 1, B, A), d_values_of(grads, T + 1, B, A)};
 }
 
+// vtrace.from_importance_weights (vtrace.py:164-280) for the plain case: five
+// contiguous float32 CUDA tensors, [T, B] and [B].  Everything else (trailing
+// dimensions, other dtypes, host data) stays with the Python wrapper.
+// Python: (vs, pg_advantages)
+std::vector<Tensor> importance_weights(const Tensor& log_rhos, const Tensor& discounts, const Tensor& rewards,
+                                       const Tensor& values, const Tensor& bootstrap,
+                                       c10::optional<double> clip_rho, c10::optional<double> clip_pg_rho) {
+  TORCH_CHECK(g_abi.importance_weights != nullptr, "vtrace_torch_ext: vtr_from_importance_weights_f32 not bound");
+  const at::Device dev = values.device();
+  want(values, "values", at::kFloat, 2, dev);
+  want(log_rhos, "log_rhos", at::kFloat, 2, dev);
+  want(discounts, "discounts", at::kFloat, 2, dev);
+  want(rewards, "rewards", at::kFloat, 2, dev);
+  want(bootstrap, "bootstrap_value", at::kFloat, 1, dev);
+  const int64_t T = values.size(0), B = values.size(1);
+  for (const Tensor* t : {&log_rhos, &discounts, &rewards})
+    TORCH_CHECK_VALUE(t->size(0) == T && t->size(1) == B, "log_rhos, discounts and rewards must have shape [T, B] = [",
+                      T, ", ", B, "]");
+  TORCH_CHECK_VALUE(bootstrap.size(0) == B, "bootstrap_value must start with [B]");
+  TORCH_CHECK_VALUE(T > 0 && B > 0 && T * B < (int64_t(1) << 31), "bad shape");
+  c10::cuda::CUDAGuard guard(dev);
+  Tensor out = at::empty({2, T, B}, values.options());
+  const uint32_t flags = (clip_rho ? 0u : VTR_FLAG_NO_CLIP_RHO) | (clip_pg_rho ? 0u : VTR_FLAG_NO_CLIP_PG_RHO);
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev.index()).stream();
+  check(g_abi.importance_weights(log_rhos.data_ptr<float>(), discounts.data_ptr<float>(), rewards.data_ptr<float>(),
+                                 values.data_ptr<float>(), bootstrap.data_ptr<float>(), static_cast<int32_t>(T),
+                                 static_cast<int32_t>(B), 1, 0u, clip_rho ? static_cast<float>(*clip_rho) : 0.0f,
+                                 clip_pg_rho ? static_cast<float>(*clip_pg_rho) : 0.0f, flags,
+                                 out.data_ptr<float>(), out.data_ptr<float>() + T * B, stream),
+        "vtr_from_importance_weights_f32");
+  return {out.select(0, 0), out.select(0, 1)};
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("bind", &bind, "hand over the addresses of the C ABI entry points");
   m.def("fused_loss", &fused_loss);
   m.def("fused_learner_loss", &fused_learner_loss);
+  m.def("bind_importance_weights", &bind_importance_weights);
+  m.def("importance_weights", &importance_weights);
   m.def("fused_loss_and_grads", &fused_loss_and_grads);
   m.def("fused_learner_loss_and_grads", &fused_learner_loss_and_grads);
 }
