@@ -22,7 +22,7 @@ namespace vtr {
 //   [256,512)  `warps` mbarriers "carry arrived"  (recurrence hand-off)
 //   ring       depth slots of slot_floats floats: one time step of the tile each
 //   staging    warps x 32*A floats: each warp's d_target_logits row  (GRADS only)
-//   carry      warps x 96 floats, the first 32 used: acc per lane
+//   carry      warps x 96 floats reserved, the first warps x 32 used: acc per lane
 //   sums       warps x 3 doubles: per-warp loss partials
 //
 // Launch bound 768 threads (never more than 512 are launched) caps the kernel

@@ -4,9 +4,9 @@
 // exchange per call: every rank's 4 loss scalars.  A collective library call
 // costs a kernel launch per rank plus its own rendezvous for 16 bytes; here
 // every rank stores its values straight into every peer's buffer (P2P stores
-// through NVLink / NVSwitch, buffers from torch symmetric memory) followed by a
-// sequence number, and sums what has arrived in rank order.  The sum is
-// bitwise identical on all ranks.
+// through NVLink / NVSwitch, buffers from torch symmetric memory), each value
+// in one 8-byte word together with the step's sequence number, and sums what
+// has arrived in rank order.  The sum is bitwise identical on all ranks.
 //
 // Buffer layout and the slot-reuse argument: exchange.cuh.
 #include "common.h"

@@ -115,7 +115,8 @@ class LossExchange(object):
       lag=0  this step's sums: the launch ends only when the slowest rank has
              published, so every step pays the rendezvous;
       lag=1  the previous step's sums, which are normally in this rank's buffer
-             already: no rank waits for another (nothing is written on the
+             already and are fetched at the start of the launch, next to the
+             streaming: no rank waits for another (nothing is written on the
              first step; fetch the last step's sums with `collect()`).
 
     Without `sums`, follow the fused call with `collect()` on the same stream.
