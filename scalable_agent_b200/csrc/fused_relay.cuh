@@ -28,10 +28,13 @@ namespace vtr {
 // Launch bound 768 threads (never more than 512 are launched) caps the kernel
 // at 80 registers, so that 24 warps fit an SM's register file.
 // ---------------------------------------------------------------------------
-template <int A_CT, bool GRADS>
-// 768 threads per SM is what the host makes resident (24 warps: one tile of 16,
-// two of 12, three of 8 ...), so the register budget is that of 768 threads.
-__global__ void __launch_bounds__(768) fused_relay_kernel(const __grid_constant__ TileArgs args) {
+// 768 threads per SM is what the host makes resident (24 warps: two tiles of
+// 12, three of 8 ...), so the register budget is that of 768 threads - except
+// for a tile that has its SM to itself (SOLO: 16 warps, 128 registers), where
+// fewer values have to be recomputed or re-read from the parameter bank in
+// every step of a loop that is bound by instruction issue.
+template <int A_CT, bool GRADS, bool SOLO = false>
+__global__ void __launch_bounds__(SOLO ? 512 : 768) fused_relay_kernel(const __grid_constant__ TileArgs args) {
   const FusedArgs& a = args.f;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int A = A_CT > 0 ? A_CT : a.A;

@@ -147,7 +147,11 @@ static int launch_tiles(const TileArgs& args, int tiles, int warps, size_t smem,
                                       : "");
     return VTR_OK;
   }
-  auto kernel = warps > 1 ? fused_relay_kernel<A_CT, GRADS> : fused_column_kernel<A_CT, GRADS>;
+  DeviceInfo dev;
+  const bool solo = warps > 1 && warps <= 16 && device_info(&dev) == VTR_OK && tiles <= dev.sm_count &&
+                    !getenv("VTR_RELAY_NO_SOLO");
+  auto kernel = warps > 1 ? (solo ? fused_relay_kernel<A_CT, GRADS, true> : fused_relay_kernel<A_CT, GRADS, false>)
+                          : fused_column_kernel<A_CT, GRADS>;
   if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
   LaunchConfig l;
   launch_config(l, dim3(tiles), dim3(32 * warps), smem, stream);
