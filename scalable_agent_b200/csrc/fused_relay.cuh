@@ -33,8 +33,12 @@ namespace vtr {
 // for a tile that has its SM to itself (SOLO: 16 warps, 128 registers), where
 // fewer values have to be recomputed or re-read from the parameter bank in
 // every step of a loop that is bound by instruction issue.
-template <int A_CT, bool GRADS, bool SOLO = false>
-__global__ void __launch_bounds__(SOLO ? 512 : 768) fused_relay_kernel(const __grid_constant__ TileArgs args) {
+// DUO: two tiles of up to 10 warps per SM, 96 registers each.
+enum RelayBudget { kRelayShared = 0, kRelaySolo = 1, kRelayDuo = 2 };
+template <int A_CT, bool GRADS, int BUDGET = kRelayShared>
+__global__ void __launch_bounds__(BUDGET == kRelaySolo ? 512 : (BUDGET == kRelayDuo ? 320 : 768),
+                                  BUDGET == kRelayDuo ? 2 : 1)
+    fused_relay_kernel(const __grid_constant__ TileArgs args) {
   const FusedArgs& a = args.f;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int A = A_CT > 0 ? A_CT : a.A;

@@ -148,9 +148,12 @@ static int launch_tiles(const TileArgs& args, int tiles, int warps, size_t smem,
     return VTR_OK;
   }
   DeviceInfo dev;
-  const bool solo = warps > 1 && warps <= 16 && device_info(&dev) == VTR_OK && tiles <= dev.sm_count &&
-                    !getenv("VTR_RELAY_NO_SOLO");
-  auto kernel = warps > 1 ? (solo ? fused_relay_kernel<A_CT, GRADS, true> : fused_relay_kernel<A_CT, GRADS, false>)
+  const bool known = device_info(&dev) == VTR_OK && !getenv("VTR_RELAY_NO_SOLO");
+  const bool solo = known && warps > 1 && warps <= 16 && tiles <= dev.sm_count;
+  const bool duo = known && !solo && warps > 1 && warps <= 10 && tiles <= 2 * dev.sm_count;
+  auto kernel = warps > 1 ? (solo ? fused_relay_kernel<A_CT, GRADS, kRelaySolo>
+                                  : (duo ? fused_relay_kernel<A_CT, GRADS, kRelayDuo>
+                                         : fused_relay_kernel<A_CT, GRADS, kRelayShared>))
                           : fused_column_kernel<A_CT, GRADS>;
   if (int rc = allow_dynamic_smem(reinterpret_cast<const void*>(kernel), smem)) return rc;
   LaunchConfig l;
@@ -702,6 +705,9 @@ static int run_column_path(const vtr_fused_params* p, double* partials, cudaStre
   // 166 us with 3 warps and 4 slots); below that, aim at ~24 warps per SM while
   // the ring still runs at least 2 slots ahead of the warps.
   int warps = resident >= 7 ? 1 : 24 / resident;
+  // Two tiles per SM: 10 warps each instead of 12 buys the kernel 96 registers
+  // instead of 80 (the DUO variant of K1b).
+  if (resident == 2 && !getenv("VTR_RELAY_NO_SOLO")) warps = 10;
   if (const int forced = env_int("VTR_COLUMN_WARPS")) warps = forced;
   if (warps > kRelayMaxWarps) warps = kRelayMaxWarps;
   if (warps > p->T) warps = p->T;
