@@ -346,9 +346,12 @@ def run_gpu(args):
     B //= world
   K, W = args.steps, args.warmup
   # The per-SM speed table behind the tile sizes is a running mean over an
-  # SM's first 20 tiles: an unreported pre-pass makes sure it has settled
-  # whatever --warmup is (its length is in the line, run.untimed_pre_pass_steps).
-  PRE = max(0, 30 - W)
+  # SM's first 20 tiles and an exponential mean (weight 0.05) after that: an
+  # unreported pre-pass lets it settle whatever --warmup is (its length is in
+  # the line, run.untimed_pre_pass_steps).  Measured with --steps 20 --warmup 5:
+  # 30 steps before the timed region 144.2 us per step, 100 steps 143.4, 300
+  # steps 143.1 (a learner runs for millions of steps; 100 steps are 14 ms).
+  PRE = max(0, int(os.environ.get('VTR_BENCH_PRE', '100')) - W)
 
   # Inputs + outputs of one step must not fit the 126 MB L2, or steps would be
   # served from it: small per-GPU batches (strong scaling) rotate over several
